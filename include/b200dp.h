@@ -1,0 +1,212 @@
+/*
+ * b200dp.h -- C ABI of libb200dp.so: the B200-native (sm_100a) data-parallel hot path.
+ *
+ * The path (BASELINE.json north_star): every training step the
+ * reference scripts hand ~214 fp32 gradient tensors (Keras ResNet-50, 25,583,592
+ * elements) to a cross-replica SUM and then to the optimizer.  The reference reaches
+ * that through three glue layers, none of which it implements itself:
+ *   - tf.distribute.MirroredStrategy()            imagenet-resnet50-mirror.py:21   (fit :81)
+ *   - MultiWorkerMirroredStrategy(NCCL)           imagenet-resnet50-multiworkers.py:20-25 (fit :95)
+ *   - hvd.DistributedOptimizer(Adam)              imagenet-resnet50-hvd.py:99-101  (fit :120)
+ *   - ParameterServerStrategy push/pull           imagenet-resnet50-ps.py:75-82    (fit :142)
+ *   - compile(optimizer='adam')                   imagenet-resnet50-mirror.py:76, imagenet-resnet50.py:62
+ * This library is what a binding for those layers calls instead of
+ * {concat, ncclAllReduce, split, 214 x ResourceApplyAdam}.  Each entry point below
+ * cites the reference interface it stands in for.
+ *
+ * Conventions
+ *   - plain C, no exceptions; every function returns b2dp_status (0 ok, <0 error) and
+ *     b2dp_last_error() gives a thread-local message for the last failure;
+ *   - tensor memory that crosses the boundary is caller-owned device memory; the library
+ *     owns only its flat symmetric buffers, flag words, optimizer-state shards and tables;
+ *   - work is enqueued on the caller's cudaStream_t (passed as void*) and the call returns
+ *     without a host sync;
+ *   - there is no CPU fallback: contexts can only be created on an sm_100 device.
+ *   - "rank" r of a context is GPU r of the job.  A *local* context drives all ranks from
+ *     one process (MirroredStrategy's shape); a *rank* context drives one (Horovod /
+ *     MultiWorkerMirroredStrategy's shape, one process per GPU).  `dev` below is the index
+ *     of the rank inside the context: 0..n-1 for a local context, always 0 for a rank one.
+ *   - collective entry points (step, allreduce, all_gather) must be called for every rank,
+ *     in the same order, like NCCL calls.
+ */
+#ifndef B200DP_H_
+#define B200DP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  B2DP_OK = 0,
+  B2DP_ERR_INVALID = -1,   /* bad argument / mismatched shapes (the glue raises ValueError) */
+  B2DP_ERR_CUDA = -2,      /* a CUDA runtime or driver call failed */
+  B2DP_ERR_NO_DEVICE = -3, /* no usable CUDA device */
+  B2DP_ERR_ARCH = -4,      /* device is not sm_100 */
+  B2DP_ERR_STATE = -5,     /* call made in the wrong state (e.g. peers not attached) */
+  B2DP_ERR_TIMEOUT = -6,   /* a cross-GPU flag wait gave up */
+  B2DP_ERR_SYS = -7,       /* socket / OS failure in the fd exchange helper */
+  B2DP_ERR_TOO_LARGE = -8  /* size beyond a documented fixed maximum */
+} b2dp_status;
+
+typedef enum { B2DP_F32 = 0, B2DP_BF16 = 1 } b2dp_dtype;
+
+typedef enum { B2DP_OPT_NONE = 0, B2DP_OPT_ADAM = 1, B2DP_OPT_SGDM = 2 } b2dp_opt;
+
+/* Which flat buffer an accessor / unpack refers to. */
+typedef enum {
+  B2DP_BUF_GRADS = 0,   /* wire-format gradient bucket buffer (f32 or bf16), symmetric */
+  B2DP_BUF_WEIGHTS = 1, /* fp32 mirrored weights, symmetric */
+  B2DP_BUF_REDUCED = 2, /* fp32 all-reduced gradients (== GRADS when the wire is f32) */
+  B2DP_BUF_STATE0 = 3,  /* this rank's shard of Adam m / SGD momentum accumulator */
+  B2DP_BUF_STATE1 = 4,  /* this rank's shard of Adam v */
+  B2DP_BUF_STATS = 5    /* 4 doubles, see b2dp_step */
+} b2dp_buf;
+
+/* Hyper-parameters are per-call: the scripts' callbacks mutate the learning rate while
+ * training (ReduceLROnPlateau imagenet-resnet50-mirror.py:78; LearningRateWarmupCallback
+ * imagenet-resnet50-hvd.py:115) and Adam's bias correction depends on the step. */
+typedef struct {
+  float lr;           /* Adam / SGD learning rate */
+  float beta1;        /* Adam */
+  float beta2;        /* Adam */
+  float eps;          /* Adam (Keras default 1e-7) */
+  float momentum;     /* SGD mu */
+  float weight_decay; /* SGD decoupled weight decay lambda (0 = off) */
+  int32_t nesterov;   /* SGD */
+  int32_t want_stats; /* !=0: also produce the B2DP_BUF_STATS words for this rank's shard */
+  int64_t step;       /* 1-based optimizer step (Adam bias correction) */
+  float postscale;    /* multiplies the reduced sum before the optimizer (1/n for hvd Average) */
+  float reserved;
+} b2dp_hyper;
+
+typedef struct b2dp_layout b2dp_layout;
+typedef struct b2dp_ctx b2dp_ctx;
+typedef struct b2dp_plan b2dp_plan;
+
+const char* b2dp_last_error(void);
+/* ABI version of this header; bumps when a signature changes. */
+int b2dp_abi_version(void);
+
+/* ---------------------------------------------------------------- layout (host only) --
+ * The gradient bucketing layer.  Stands in for tf.distribute's _pack_tensors /
+ * group_by_size(bytes_per_pack) [CommunicationOptions, imagenet-resnet50-multiworkers.py:20-21]
+ * and Horovod's fusion buffer (HOROVOD_FUSION_THRESHOLD) [imagenet-resnet50-hvd.py:101].
+ * K tensors in the caller's order are laid end to end, each start aligned to 32 elements;
+ * a bucket closes when the next tensor would push it past bucket_bytes (0 = one bucket,
+ * the reference default); each bucket is padded so it cuts into nranks equal slices of a
+ * multiple of 256 elements.  Rank r owns slice r of every bucket.  Pure host arithmetic:
+ * usable (and tested) without a GPU. */
+int b2dp_layout_create(int32_t num_tensors, const int64_t* numel, int32_t nranks,
+                       int32_t wire_dtype, int64_t bucket_bytes, b2dp_layout** out);
+void b2dp_layout_destroy(b2dp_layout* l);
+int32_t b2dp_layout_num_tensors(const b2dp_layout* l);
+int32_t b2dp_layout_num_buckets(const b2dp_layout* l);
+int32_t b2dp_layout_nranks(const b2dp_layout* l);
+int64_t b2dp_layout_total_elems(const b2dp_layout* l);  /* padded flat length */
+int64_t b2dp_layout_shard_elems(const b2dp_layout* l);  /* optimizer-state elements per rank */
+int64_t b2dp_layout_tensor_offset(const b2dp_layout* l, int32_t k); /* flat element offset */
+int32_t b2dp_layout_tensor_bucket(const b2dp_layout* l, int32_t k);
+/* info[0]=first tensor, [1]=tensor count, [2]=flat offset, [3]=padded elems,
+ * [4]=slice elems (per rank), [5]=offset of this bucket inside a rank's state shard */
+int b2dp_layout_bucket_info(const b2dp_layout* l, int32_t b, int64_t info[6]);
+
+/* ------------------------------------------------------------------------- context --
+ * Local context: one process, ndev GPUs, peer access through one address space --
+ * MirroredStrategy() (imagenet-resnet50-mirror.py:21).  Listing the same device more
+ * than once gives *emulated ranks* on one GPU: the collective kernels then run without
+ * cross-GPU flag waits and the caller must issue each collective call for ranks 0..n-1
+ * back to back on one stream (used to check the n-rank arithmetic on a 1-GPU box). */
+int b2dp_ctx_create_local(int32_t ndev, const int32_t* devices, b2dp_ctx** out);
+/* Rank context: this process drives GPU `device` as rank `rank` of `nranks` --
+ * hvd.init() + local_rank pinning (imagenet-resnet50-hvd.py:16,36-41) and one MWMS
+ * worker (imagenet-resnet50-multiworkers.py:24-25). */
+int b2dp_ctx_create_rank(int32_t rank, int32_t nranks, int32_t device, b2dp_ctx** out);
+void b2dp_ctx_destroy(b2dp_ctx* c);
+int32_t b2dp_ctx_nranks(const b2dp_ctx* c);
+int32_t b2dp_ctx_num_local(const b2dp_ctx* c);
+/* Seconds a cross-GPU flag wait may spin before the kernel gives up (default 10). */
+int b2dp_ctx_set_timeout(b2dp_ctx* c, double seconds);
+
+/* ---------------------------------------------------------------------------- plan --
+ * Binds a layout to a context: allocates, per local rank, one peer-mappable block
+ * holding flags | gradient buckets | mirrored weights | reduced gradients | state shards.
+ * For a local context the peer mapping is done here.  For a rank context the caller
+ * moves one POSIX fd per rank between processes (b2dp_fd_exchange below, or any
+ * SCM_RIGHTS / pidfd_getfd transport) and attaches each peer. */
+int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** out);
+void b2dp_plan_destroy(b2dp_plan* p);
+int b2dp_plan_export_fd(b2dp_plan* p, int* fd_out);            /* rank context only */
+int b2dp_plan_attach_peer(b2dp_plan* p, int32_t peer_rank, int fd); /* rank context only */
+int32_t b2dp_plan_ready(const b2dp_plan* p);                   /* 1 once every peer is mapped */
+/* Device pointer of one of the plan's flat buffers on local rank `dev` (aliasable: a
+ * harness may make its variables views of B2DP_BUF_WEIGHTS and skip unpack). */
+int b2dp_plan_buffer(b2dp_plan* p, int32_t dev, int32_t which, void** ptr, int64_t* elems);
+/* Reads and clears the device-side status word of rank `dev` (host sync on `stream`):
+ * B2DP_OK or B2DP_ERR_TIMEOUT. */
+int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream);
+
+/* --------------------------------------------------------------------- the hot path --
+ * (1) pack: gather + cast + prescale the bucket's gradient tensors into the wire buffer.
+ * One launch over a device-resident (pointer, offset, count) tile table.  Replaces
+ * cross_device_ops._pack_tensors/concat (MirroredStrategy, -mirror.py:21) and Horovod's
+ * batched_memcpy_k + prescale into the fusion buffer (-hvd.py:101).  `grads` is a HOST
+ * array of K device pointers (all tensors of the plan, index = tensor id; only the
+ * bucket's are read); bucket < 0 packs every bucket. */
+int b2dp_pack(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads,
+              int32_t grad_dtype, float prescale, void* stream);
+
+/* (2)+(3) step: reduce-scatter(SUM) the bucket across ranks -- rank r pulls slice r from
+ * every rank's wire buffer and adds in rank order 0..n-1 in fp32, which is TF's
+ * ReductionToOneDevice/AddN order -- then applies the optimizer to rank r's shard of
+ * (w, state) in registers, and all-gathers by storing the updated weights into every
+ * rank's weight buffer.  One kernel; flag barriers at entry and exit.  Replaces
+ * batch_reduce(SUM) + 214 ResourceApplyAdam launches (-mirror.py:76,81), the
+ * CollectiveReduceV2 path (-multiworkers.py:20-25,95) and, with slices as PS shards,
+ * the PS push/apply/pull (-ps.py:75-82,142).  With n == 1 it is the optimizer apply
+ * alone (imagenet-resnet50.py:62,67).  opt == B2DP_OPT_NONE is rejected (use allreduce).
+ * hyper->want_stats: B2DP_BUF_STATS[0] = sum of squares of the reduced gradient over
+ * this rank's shard, [1] = count of non-finite reduced-gradient elements. */
+int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp_hyper* hyper,
+              void* stream);
+
+/* hvd-compatible allreduce: same reduce-scatter + all-gather with no optimizer; the
+ * result (sum * postscale, fp32) lands in B2DP_BUF_REDUCED of every rank.  Replaces
+ * hvd.allreduce(op=Average|Sum) under hvd.DistributedOptimizer (-hvd.py:101) and
+ * CrossDeviceOps.batch_reduce_implementation for non-variable destinations. */
+int b2dp_allreduce(b2dp_plan* p, int32_t dev, int32_t bucket, float postscale, void* stream);
+
+/* The two halves of step as separate launches (PS push = reduce_scatter_apply, pull =
+ * all_gather; -ps.py:75-82).  all_gather pushes this rank's weight slice to all peers. */
+int b2dp_reduce_scatter_apply(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt,
+                              const b2dp_hyper* hyper, void* stream);
+int b2dp_all_gather(b2dp_plan* p, int32_t dev, int32_t bucket, void* stream);
+
+/* unpack: scatter a flat buffer (B2DP_BUF_WEIGHTS or B2DP_BUF_REDUCED) back into the
+ * caller's K tensors (fp32).  Replaces array_ops.split after the all-reduce
+ * (-mirror.py:81) and Horovod's memcpy-out of the fusion buffer (-hvd.py:101).
+ * pack's inverse for initial weights: b2dp_load_weights gathers K fp32 tensors into
+ * B2DP_BUF_WEIGHTS (hvd BroadcastGlobalVariables-style initial sync is a step-0 concern
+ * of the glue, -hvd.py:111). */
+int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t which, void* const* outs,
+                void* stream);
+int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* weights, void* stream);
+
+/* Scalar the Adam kernel multiplies by: lr*sqrt(1-beta2^t)/(1-beta1^t) in fp32, exposed
+ * so a checker can use the library's exact value. */
+float b2dp_adam_alpha(float lr, float beta1, float beta2, int64_t step);
+
+/* ----------------------------------------------------------- rank bootstrap helper --
+ * Moves one fd per rank between the processes of a job over abstract unix datagram
+ * sockets (SCM_RIGHTS).  `session` must be the same string on every rank and unique to
+ * the job (e.g. MASTER_PORT + a counter).  peer_fds[r] receives rank r's fd
+ * (peer_fds[rank] = dup of my_fd).  Host-only; works for any fd. */
+int b2dp_fd_exchange(int32_t rank, int32_t nranks, const char* session, int my_fd,
+                     int* peer_fds, int32_t timeout_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H_ */

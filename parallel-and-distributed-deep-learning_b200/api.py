@@ -1,0 +1,236 @@
+"""Host-side mirror of the C ABI: Layout, Context, Plan.
+
+Thin by design -- each method is one C call.  torch is used only for what the task
+allows it for: device memory handed in by the caller, streams, and (in glue modules)
+torch.distributed for rendezvous.  Every compute call lands in libb200dp.so.
+"""
+import ctypes
+import os
+
+from . import _lib
+from ._lib import (BF16, BUF_GRADS, BUF_REDUCED, BUF_STATE0, BUF_STATE1, BUF_STATS, BUF_WEIGHTS, F32, OPT_ADAM,
+                   OPT_NONE, OPT_SGDM, B200dpError, Hyper, check)
+
+_DTYPES = {"f32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16, F32: F32, BF16: BF16}
+_OPTS = {"adam": OPT_ADAM, "sgdm": OPT_SGDM, "sgd": OPT_SGDM, "none": OPT_NONE,
+         OPT_ADAM: OPT_ADAM, OPT_SGDM: OPT_SGDM, OPT_NONE: OPT_NONE}
+
+
+def adam_hyper(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-7, step=1, postscale=1.0, want_stats=False):
+    """Keras Adam defaults (compile(optimizer='adam'), imagenet-resnet50-mirror.py:76)."""
+    return Hyper(lr=lr, beta1=beta1, beta2=beta2, eps=eps, momentum=0.0, weight_decay=0.0, nesterov=0,
+                 want_stats=int(bool(want_stats)), step=int(step), postscale=postscale, reserved=0.0)
+
+
+def sgdm_hyper(lr=0.01, momentum=0.9, nesterov=False, weight_decay=0.0, postscale=1.0, want_stats=False):
+    return Hyper(lr=lr, beta1=0.0, beta2=0.0, eps=0.0, momentum=momentum, weight_decay=weight_decay,
+                 nesterov=int(bool(nesterov)), want_stats=int(bool(want_stats)), step=1, postscale=postscale,
+                 reserved=0.0)
+
+
+def adam_alpha(lr, beta1, beta2, step):
+    return float(_lib.load().b2dp_adam_alpha(lr, beta1, beta2, int(step)))
+
+
+class Layout:
+    """The bucketing layer: K tensors -> buckets -> per-rank slices (host arithmetic only)."""
+
+    def __init__(self, numels, nranks=1, wire="f32", bucket_bytes=0):
+        L = _lib.load()
+        numels = [int(x) for x in numels]
+        arr = (ctypes.c_int64 * max(1, len(numels)))(*numels)
+        h = ctypes.c_void_p()
+        try:
+            wire_id = _DTYPES[wire]
+        except KeyError:
+            raise ValueError("wire dtype must be f32 or bf16, got %r" % (wire,))
+        rc = L.b2dp_layout_create(len(numels), arr, int(nranks), wire_id, int(bucket_bytes), ctypes.byref(h))
+        if rc == _lib.ERR_INVALID:
+            raise ValueError(L.b2dp_last_error().decode())
+        check(rc)
+        self._h = h
+        self.numels = numels
+        self.nranks = int(nranks)
+        self.wire = wire_id
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.load().b2dp_layout_destroy(h)
+
+    num_tensors = property(lambda s: _lib.load().b2dp_layout_num_tensors(s._h))
+    num_buckets = property(lambda s: _lib.load().b2dp_layout_num_buckets(s._h))
+    total_elems = property(lambda s: _lib.load().b2dp_layout_total_elems(s._h))
+    shard_elems = property(lambda s: _lib.load().b2dp_layout_shard_elems(s._h))
+
+    def tensor_offset(self, k):
+        return check(_lib.load().b2dp_layout_tensor_offset(self._h, k))
+
+    def tensor_bucket(self, k):
+        return check(_lib.load().b2dp_layout_tensor_bucket(self._h, k))
+
+    def bucket_info(self, b):
+        info = (ctypes.c_int64 * 6)()
+        rc = _lib.load().b2dp_layout_bucket_info(self._h, b, info)
+        if rc == _lib.ERR_INVALID:
+            raise ValueError(_lib.load().b2dp_last_error().decode())
+        check(rc)
+        keys = ("first", "count", "offset", "elems", "slice", "shard_off")
+        return dict(zip(keys, (int(x) for x in info)))
+
+
+class Context:
+    def __init__(self, handle, nranks, ranks, devices, local):
+        self._h = handle
+        self.nranks = nranks
+        self.ranks = list(ranks)      # global rank of each local slot
+        self.devices = list(devices)  # CUDA device of each local slot
+        self.is_local = local
+
+    @classmethod
+    def local(cls, devices):
+        """One process drives all ranks (MirroredStrategy(), imagenet-resnet50-mirror.py:21).
+        Repeating a device id gives emulated ranks on one GPU."""
+        devices = [int(d) for d in devices]
+        arr = (ctypes.c_int32 * len(devices))(*devices)
+        h = ctypes.c_void_p()
+        check(_lib.load().b2dp_ctx_create_local(len(devices), arr, ctypes.byref(h)))
+        return cls(h, len(devices), range(len(devices)), devices, True)
+
+    @classmethod
+    def rank(cls, rank, nranks, device):
+        """One process per GPU (hvd.init(), imagenet-resnet50-hvd.py:16; one MWMS worker,
+        imagenet-resnet50-multiworkers.py:24-25)."""
+        h = ctypes.c_void_p()
+        check(_lib.load().b2dp_ctx_create_rank(int(rank), int(nranks), int(device), ctypes.byref(h)))
+        return cls(h, int(nranks), [int(rank)], [int(device)], False)
+
+    def set_timeout(self, seconds):
+        check(_lib.load().b2dp_ctx_set_timeout(self._h, float(seconds)))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.load().b2dp_ctx_destroy(h)
+
+
+class _DevMem:
+    """__cuda_array_interface__ carrier so torch can view a library-owned buffer."""
+
+    def __init__(self, ptr, shape, typestr, owner):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+def _stream_handle(stream, device):
+    if stream is None:
+        import torch
+        return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    if hasattr(stream, "cuda_stream"):
+        return ctypes.c_void_p(stream.cuda_stream)
+    return ctypes.c_void_p(int(stream))
+
+
+def _ptr_array(tensors_or_ptrs):
+    vals = [int(t.data_ptr()) if hasattr(t, "data_ptr") else int(t) for t in tensors_or_ptrs]
+    return (ctypes.c_void_p * max(1, len(vals)))(*vals)
+
+
+class Plan:
+    """A layout bound to a context: owns the symmetric buffers and issues the hot path."""
+
+    def __init__(self, ctx, layout):
+        self.ctx = ctx
+        self.layout = layout
+        h = ctypes.c_void_p()
+        check(_lib.load().b2dp_plan_create(ctx._h, layout._h, ctypes.byref(h)))
+        self._h = h
+        self._L = _lib.load()
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.load().b2dp_plan_destroy(h)
+
+    # -- bootstrap (rank contexts) ----------------------------------------------------
+    def exchange(self, session, timeout_ms=60000):
+        """Moves every rank's block fd to every other rank and maps the peers."""
+        if self.ctx.is_local or self.ctx.nranks == 1:
+            return
+        fd = ctypes.c_int(-1)
+        check(self._L.b2dp_plan_export_fd(self._h, ctypes.byref(fd)))
+        n, rank = self.ctx.nranks, self.ctx.ranks[0]
+        fds = (ctypes.c_int * n)()
+        try:
+            check(self._L.b2dp_fd_exchange(rank, n, str(session).encode(), fd.value, fds, int(timeout_ms)))
+            for r in range(n):
+                if r != rank:
+                    check(self._L.b2dp_plan_attach_peer(self._h, r, fds[r]))
+        finally:
+            os.close(fd.value)
+            for r in range(n):
+                if fds[r] >= 0:
+                    os.close(fds[r])
+
+    @property
+    def ready(self):
+        return bool(self._L.b2dp_plan_ready(self._h))
+
+    # -- buffers -----------------------------------------------------------------------
+    def buffer_ptr(self, dev, which):
+        p, n = ctypes.c_void_p(), ctypes.c_int64()
+        check(self._L.b2dp_plan_buffer(self._h, dev, which, ctypes.byref(p), ctypes.byref(n)))
+        return int(p.value or 0), int(n.value)
+
+    def tensor(self, dev, which):
+        """torch view (no copy) of one of the plan's flat buffers on local rank `dev`."""
+        import torch
+        ptr, n = self.buffer_ptr(dev, which)
+        if which == BUF_STATS:
+            typestr, dt = "<f8", torch.float64
+        elif which == BUF_GRADS and self.layout.wire == BF16:
+            typestr, dt = "<i2", torch.bfloat16
+        else:
+            typestr, dt = "<f4", torch.float32
+        device = "cuda:%d" % self.ctx.devices[dev]
+        if n == 0:
+            return torch.empty(0, dtype=dt, device=device)
+        t = torch.as_tensor(_DevMem(ptr, (n,), typestr, self), device=device)
+        return t.view(dt) if t.dtype != dt else t
+
+    # -- the hot path --------------------------------------------------------------------
+    def pack(self, dev, grads, prescale=1.0, bucket=-1, stream=None):
+        if len(grads) != self.layout.num_tensors:
+            raise ValueError("pack: %d tensors, plan has %d" % (len(grads), self.layout.num_tensors))
+        check(self._L.b2dp_pack(self._h, dev, bucket, _ptr_array(grads), F32, prescale,
+                                _stream_handle(stream, self.ctx.devices[dev])))
+
+    def load_weights(self, dev, weights, stream=None):
+        if len(weights) != self.layout.num_tensors:
+            raise ValueError("load_weights: %d tensors, plan has %d" % (len(weights), self.layout.num_tensors))
+        check(self._L.b2dp_load_weights(self._h, dev, _ptr_array(weights),
+                                        _stream_handle(stream, self.ctx.devices[dev])))
+
+    def unpack(self, dev, outs, which=BUF_WEIGHTS, bucket=-1, stream=None):
+        if len(outs) != self.layout.num_tensors:
+            raise ValueError("unpack: %d tensors, plan has %d" % (len(outs), self.layout.num_tensors))
+        check(self._L.b2dp_unpack(self._h, dev, bucket, which, _ptr_array(outs),
+                                  _stream_handle(stream, self.ctx.devices[dev])))
+
+    def step(self, dev, opt, hyper, bucket=-1, stream=None):
+        check(self._L.b2dp_step(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
+                                _stream_handle(stream, self.ctx.devices[dev])))
+
+    def reduce_scatter_apply(self, dev, opt, hyper, bucket=-1, stream=None):
+        check(self._L.b2dp_reduce_scatter_apply(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
+                                                _stream_handle(stream, self.ctx.devices[dev])))
+
+    def all_gather(self, dev, bucket=-1, stream=None):
+        check(self._L.b2dp_all_gather(self._h, dev, bucket, _stream_handle(stream, self.ctx.devices[dev])))
+
+    def allreduce(self, dev, postscale=1.0, bucket=-1, stream=None):
+        check(self._L.b2dp_allreduce(self._h, dev, bucket, postscale,
+                                     _stream_handle(stream, self.ctx.devices[dev])))
+
+    def check(self, dev, stream=None):
+        check(self._L.b2dp_plan_check(self._h, dev, _stream_handle(stream, self.ctx.devices[dev])))

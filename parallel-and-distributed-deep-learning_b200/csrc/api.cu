@@ -1,0 +1,578 @@
+// api.cu -- contexts, plans and kernel launchers behind include/b200dp.h.
+#include <cmath>
+#include <cstring>
+#include <memory>
+
+#include <unistd.h>
+
+#include "kernels.cuh"
+
+using namespace b2dp;
+
+namespace {
+
+#define CUDA_TRY(call)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (call);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      (void)cudaGetLastError();                                                          \
+      return fail(B2DP_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_e));               \
+    }                                                                                    \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Byte map of a rank's peer-mappable block.
+struct BlockMap {
+  size_t flags = 0;      // 2 phases * kMaxBlocks * kMaxRanks u32
+  size_t ctrl = 0;       // status word, ticket, stats
+  size_t partials = 0;   // 2 doubles per block
+  size_t grads = 0, weights = 0, reduced = 0, s0 = 0, s1 = 0, end = 0;
+};
+
+constexpr size_t kCtrlStatus = 0, kCtrlTicket = 64, kCtrlStats = 128;
+
+BlockMap make_map(const b2dp_layout& l) {
+  BlockMap m;
+  const size_t wire = l.wire == B2DP_BF16 ? 2 : 4;
+  size_t off = 0;
+  m.flags = off;
+  off += align_up(size_t(2) * kMaxBlocks * kMaxRanks * sizeof(uint32_t), 4096);
+  m.ctrl = off;
+  off += 4096;
+  m.partials = off;
+  off += align_up(size_t(2) * kMaxBlocks * sizeof(double), 4096);
+  m.grads = off;
+  off += align_up((size_t)l.total * wire, 4096);
+  m.weights = off;
+  off += align_up((size_t)l.total * 4, 4096);
+  if (l.wire == B2DP_F32) {
+    m.reduced = m.grads;  // the all-reduce runs in place
+  } else {
+    m.reduced = off;
+    off += align_up((size_t)l.total * 4, 4096);
+  }
+  m.s0 = off;
+  off += align_up((size_t)l.shard * 4, 4096);
+  m.s1 = off;
+  off += align_up((size_t)l.shard * 4, 4096);
+  m.end = off;
+  return m;
+}
+
+struct PtrTable {          // device copy of a caller's K-pointer array, re-sent only on change
+  void** dev = nullptr;
+  std::vector<const void*> host;
+};
+
+struct RankState {
+  int device = -1;
+  int rank = -1;
+  VmmBlock own;
+  VmmBlock imported[kMaxRanks];
+  char* base[kMaxRanks] = {};  // every rank's block as addressable from this rank's GPU
+  bool attached[kMaxRanks] = {};
+  Tile* d_tiles = nullptr;
+  PtrTable grads, outs, weights;
+  uint32_t epoch = 0;
+  int num_sms = 0;
+};
+
+}  // namespace
+
+struct b2dp_ctx {
+  bool local = true;
+  bool emulated = false;  // same device listed more than once
+  int nranks = 1;
+  int nlocal = 1;
+  int devices[kMaxRanks] = {};
+  int ranks[kMaxRanks] = {};
+  double timeout_s = 10.0;
+};
+
+struct b2dp_plan {
+  b2dp_ctx* ctx = nullptr;
+  b2dp_layout layout;
+  BlockMap map;
+  std::vector<std::unique_ptr<RankState>> rs;
+};
+
+namespace {
+
+int check_device(int device) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    (void)cudaGetLastError();
+    return fail(B2DP_ERR_NO_DEVICE, "no CUDA device: %s (libb200dp has no CPU fallback)",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  }
+  if (device < 0 || device >= count) return fail(B2DP_ERR_INVALID, "device %d outside 0..%d", device, count - 1);
+  int major = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  if (major != 10) return fail(B2DP_ERR_ARCH, "device %d is sm_%dx; this library is built for sm_100a only", device, major);
+  return B2DP_OK;
+}
+
+int sync_table(PtrTable& t, const void* const* ptrs, int K, cudaStream_t s) {
+  if (K == 0) return B2DP_OK;
+  if (!t.dev) CUDA_TRY(cudaMalloc(&t.dev, sizeof(void*) * K));
+  if ((int)t.host.size() == K && memcmp(t.host.data(), ptrs, sizeof(void*) * K) == 0) return B2DP_OK;
+  t.host.assign(ptrs, ptrs + K);
+  // pageable source: the runtime stages it before returning, so t.host may change later
+  CUDA_TRY(cudaMemcpyAsync(t.dev, t.host.data(), sizeof(void*) * K, cudaMemcpyHostToDevice, s));
+  return B2DP_OK;
+}
+
+int get_rank(b2dp_plan* p, int dev, RankState** out) {
+  if (!p) return fail(B2DP_ERR_INVALID, "plan is null");
+  if (dev < 0 || dev >= (int)p->rs.size()) return fail(B2DP_ERR_INVALID, "dev %d outside 0..%d", dev, (int)p->rs.size() - 1);
+  *out = p->rs[dev].get();
+  return B2DP_OK;
+}
+
+int bucket_range(const b2dp_plan* p, int bucket, int* b0, int* b1) {
+  const int nb = (int)p->layout.buckets.size();
+  if (bucket < 0) {
+    *b0 = 0;
+    *b1 = nb;
+  } else if (bucket < nb) {
+    *b0 = bucket;
+    *b1 = bucket + 1;
+  } else {
+    return fail(B2DP_ERR_INVALID, "bucket %d outside 0..%d", bucket, nb - 1);
+  }
+  return B2DP_OK;
+}
+
+int pack_grid(const RankState& r, int64_t ntiles) {
+  return (int)std::min<int64_t>(ntiles, (int64_t)r.num_sms * 8);
+}
+
+template <int DIR>
+int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const void* const* ptrs,
+                size_t flat_off, int wire, float prescale, cudaStream_t s) {
+  int b0 = 0, b1 = 0;
+  if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
+  if (!ptrs && p->layout.K > 0) return fail(B2DP_ERR_INVALID, "tensor pointer array is null");
+  if (int rc = sync_table(table, ptrs, p->layout.K, s)) return rc;
+  for (int b = b0; b < b1; ++b) {
+    const Bucket& bk = p->layout.buckets[b];
+    if (bk.tile_count == 0) continue;
+    for (int k = bk.first; k < bk.first + bk.count; ++k)
+      if (p->layout.numel[k] > 0 && !ptrs[k]) return fail(B2DP_ERR_INVALID, "tensor %d pointer is null", k);
+  }
+  // buckets are adjacent in the tile table, so a range of buckets is one launch
+  const int64_t t0 = p->layout.buckets.empty() ? 0 : p->layout.buckets[b0].tile_first;
+  int64_t nt = 0;
+  for (int b = b0; b < b1; ++b) nt += p->layout.buckets[b].tile_count;
+  if (nt == 0) return B2DP_OK;
+  char* flat = r.base[r.rank] + flat_off;
+  const int grid = pack_grid(r, nt);
+  if (wire == B2DP_F32)
+    pack_kernel<float, DIR><<<grid, kPackThreads, 0, s>>>(r.d_tiles + t0, nt, table.dev, (float*)flat, prescale);
+  else
+    pack_kernel<__nv_bfloat16, DIR><<<grid, kPackThreads, 0, s>>>(r.d_tiles + t0, nt, table.dev,
+                                                                  (__nv_bfloat16*)flat, prescale);
+  CUDA_TRY(cudaGetLastError());
+  return B2DP_OK;
+}
+
+template <typename KernelT>
+int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U) {
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kStepThreads, 0) != cudaSuccess || occ < 1) {
+    (void)cudaGetLastError();
+    occ = 1;
+  }
+  int64_t want = (nvec + (int64_t)kStepThreads * U - 1) / ((int64_t)kStepThreads * U);
+  int64_t cap = std::min<int64_t>(kMaxBlocks, (int64_t)r.num_sms * occ);
+  return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+template <int N, typename WireT, int OPT>
+int launch_step_n(const RankState& r, const StepArgs& a, cudaStream_t s) {
+  constexpr int U = (N >= 8) ? 1 : 2;
+  auto kernel = step_kernel<N, WireT, OPT, U>;
+  const int grid = step_grid(kernel, r, a.nvec, U);
+  kernel<<<grid, kStepThreads, 0, s>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return B2DP_OK;
+}
+
+template <typename WireT, int OPT>
+int launch_step_w(int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
+  switch (n) {
+    case 1: return launch_step_n<1, WireT, OPT>(r, a, s);
+    case 2: return launch_step_n<2, WireT, OPT>(r, a, s);
+    case 3: return launch_step_n<3, WireT, OPT>(r, a, s);
+    case 4: return launch_step_n<4, WireT, OPT>(r, a, s);
+    case 5: return launch_step_n<5, WireT, OPT>(r, a, s);
+    case 6: return launch_step_n<6, WireT, OPT>(r, a, s);
+    case 7: return launch_step_n<7, WireT, OPT>(r, a, s);
+    case 8: return launch_step_n<8, WireT, OPT>(r, a, s);
+  }
+  return fail(B2DP_ERR_INVALID, "unsupported rank count %d", n);
+}
+
+template <int OPT>
+int launch_step_o(int wire, int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
+  if (wire == B2DP_F32) return launch_step_w<float, OPT>(n, r, a, s);
+  return launch_step_w<__nv_bfloat16, OPT>(n, r, a, s);
+}
+
+int launch_gather(int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
+  auto go = [&](auto kernel) {
+    const int grid = step_grid(kernel, r, a.nvec, 1);
+    kernel<<<grid, kStepThreads, 0, s>>>(a);
+    return cudaGetLastError();
+  };
+  cudaError_t e = cudaSuccess;
+  switch (n) {
+    case 1: return B2DP_OK;
+    case 2: e = go(gather_kernel<2>); break;
+    case 3: e = go(gather_kernel<3>); break;
+    case 4: e = go(gather_kernel<4>); break;
+    case 5: e = go(gather_kernel<5>); break;
+    case 6: e = go(gather_kernel<6>); break;
+    case 7: e = go(gather_kernel<7>); break;
+    case 8: e = go(gather_kernel<8>); break;
+    default: return fail(B2DP_ERR_INVALID, "unsupported rank count %d", n);
+  }
+  if (e != cudaSuccess) return fail(B2DP_ERR_CUDA, "gather launch: %s", cudaGetErrorString(e));
+  return B2DP_OK;
+}
+
+int fill_comm(b2dp_plan* p, RankState& r, Comm* c) {
+  const int n = p->ctx->nranks;
+  for (int i = 0; i < kMaxRanks; ++i) c->flags[i] = nullptr;
+  for (int i = 0; i < n; ++i) c->flags[i] = reinterpret_cast<uint32_t*>(r.base[i] + p->map.flags);
+  c->status = reinterpret_cast<int32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlStatus);
+  c->timeout_ns = (uint64_t)(p->ctx->timeout_s * 1e9);
+  c->rank = r.rank;
+  c->n = n;
+  c->use_flags = (n > 1 && !p->ctx->emulated) ? 1 : 0;
+  c->epoch = ++r.epoch;
+  return B2DP_OK;
+}
+
+int fill_opt(int opt, const b2dp_hyper* h, float postscale, OptScalars* o) {
+  memset(o, 0, sizeof *o);
+  o->postscale = postscale;
+  if (opt == B2DP_OPT_NONE) return B2DP_OK;
+  if (!h) return fail(B2DP_ERR_INVALID, "hyper is null");
+  o->postscale = h->postscale;
+  if (opt == B2DP_OPT_ADAM) {
+    if (h->step < 1) return fail(B2DP_ERR_INVALID, "Adam step must be >= 1 (got %lld)", (long long)h->step);
+    o->alpha = b2dp_adam_alpha(h->lr, h->beta1, h->beta2, h->step);
+    o->omb1 = 1.0f - h->beta1;
+    o->omb2 = 1.0f - h->beta2;
+    o->eps = h->eps;
+  } else if (opt == B2DP_OPT_SGDM) {
+    o->lr = h->lr;
+    o->mu = h->momentum;
+    o->wd = h->weight_decay;
+    o->nesterov = h->nesterov;
+  } else {
+    return fail(B2DP_ERR_INVALID, "unknown optimizer %d", opt);
+  }
+  return B2DP_OK;
+}
+
+// mode 0: fused step (push), 1: reduce-scatter + apply only, 2: all-reduce, 3: all-gather only
+int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper* h, float postscale, int mode,
+                   void* stream) {
+  RankState* rp = nullptr;
+  if (int rc = get_rank(p, dev, &rp)) return rc;
+  RankState& r = *rp;
+  if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  int b0 = 0, b1 = 0;
+  if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
+  OptScalars o;
+  if (int rc = fill_opt(opt, h, postscale, &o)) return rc;
+  const int n = p->ctx->nranks;
+  const size_t wire = p->layout.wire == B2DP_BF16 ? 2 : 4;
+  cudaStream_t s = (cudaStream_t)stream;
+  DeviceGuard guard(r.device);
+  for (int b = b0; b < b1; ++b) {
+    const Bucket& bk = p->layout.buckets[b];
+    if (bk.slice == 0) continue;
+    StepArgs a;
+    memset(&a, 0, sizeof a);
+    const size_t slice_elem0 = (size_t)bk.offset + (size_t)r.rank * bk.slice;
+    const size_t out_off = (mode == 2) ? p->map.reduced : p->map.weights;
+    for (int i = 0; i < n; ++i) {
+      a.g[i] = r.base[i] + p->map.grads + slice_elem0 * wire;
+      a.out[i] = reinterpret_cast<float*>(r.base[i] + out_off + slice_elem0 * 4);
+    }
+    a.w = a.out[r.rank];
+    a.s0 = reinterpret_cast<float*>(r.base[r.rank] + p->map.s0 + (size_t)bk.shard_off * 4);
+    a.s1 = reinterpret_cast<float*>(r.base[r.rank] + p->map.s1 + (size_t)bk.shard_off * 4);
+    a.nvec = bk.slice / 4;
+    a.o = o;
+    a.partials = reinterpret_cast<double*>(r.base[r.rank] + p->map.partials);
+    a.ticket = reinterpret_cast<uint32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlTicket);
+    a.stats = reinterpret_cast<double*>(r.base[r.rank] + p->map.ctrl + kCtrlStats);
+    a.want_stats = (h && h->want_stats) ? 1 : 0;
+    a.push = (mode == 1) ? 0 : 1;
+    fill_comm(p, r, &a.c);
+    int rc;
+    if (mode == 3)
+      rc = launch_gather(n, r, a, s);
+    else if (opt == B2DP_OPT_ADAM)
+      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, s);
+    else if (opt == B2DP_OPT_SGDM)
+      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, s);
+    else
+      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, s);
+    if (rc) return rc;
+  }
+  return B2DP_OK;
+}
+
+void destroy_rank(RankState& r) {
+  if (r.device < 0) return;
+  DeviceGuard guard(r.device);
+  cudaDeviceSynchronize();
+  if (r.d_tiles) cudaFree(r.d_tiles);
+  for (PtrTable* t : {&r.grads, &r.outs, &r.weights})
+    if (t->dev) cudaFree(t->dev);
+  for (auto& b : r.imported) vmm_free(&b);
+  vmm_free(&r.own);
+  (void)cudaGetLastError();
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------ context
+extern "C" int b2dp_ctx_create_local(int32_t ndev, const int32_t* devices, b2dp_ctx** out) {
+  if (!out) return fail(B2DP_ERR_INVALID, "ctx_create_local: out is null");
+  *out = nullptr;
+  if (ndev < 1 || ndev > kMaxRanks || !devices)
+    return fail(B2DP_ERR_INVALID, "ctx_create_local: ndev %d outside 1..%d", ndev, kMaxRanks);
+  auto c = std::make_unique<b2dp_ctx>();
+  c->local = true;
+  c->nranks = c->nlocal = ndev;
+  for (int i = 0; i < ndev; ++i) {
+    if (int rc = check_device(devices[i])) return rc;
+    c->devices[i] = devices[i];
+    c->ranks[i] = i;
+    for (int j = 0; j < i; ++j) c->emulated |= (devices[j] == devices[i]);
+  }
+  if (int rc = vmm_init()) return rc;
+  *out = c.release();
+  return B2DP_OK;
+}
+
+extern "C" int b2dp_ctx_create_rank(int32_t rank, int32_t nranks, int32_t device, b2dp_ctx** out) {
+  if (!out) return fail(B2DP_ERR_INVALID, "ctx_create_rank: out is null");
+  *out = nullptr;
+  if (nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks)
+    return fail(B2DP_ERR_INVALID, "ctx_create_rank: rank %d of %d (at most %d ranks)", rank, nranks, kMaxRanks);
+  if (int rc = check_device(device)) return rc;
+  if (int rc = vmm_init()) return rc;
+  auto c = std::make_unique<b2dp_ctx>();
+  c->local = false;
+  c->nranks = nranks;
+  c->nlocal = 1;
+  c->devices[0] = device;
+  c->ranks[0] = rank;
+  *out = c.release();
+  return B2DP_OK;
+}
+
+extern "C" void b2dp_ctx_destroy(b2dp_ctx* c) { delete c; }
+extern "C" int32_t b2dp_ctx_nranks(const b2dp_ctx* c) { return c ? c->nranks : -1; }
+extern "C" int32_t b2dp_ctx_num_local(const b2dp_ctx* c) { return c ? c->nlocal : -1; }
+extern "C" int b2dp_ctx_set_timeout(b2dp_ctx* c, double seconds) {
+  if (!c || !(seconds > 0)) return fail(B2DP_ERR_INVALID, "set_timeout: need a context and seconds > 0");
+  c->timeout_s = seconds;
+  return B2DP_OK;
+}
+
+// --------------------------------------------------------------------------------- plan
+extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** out) {
+  if (!out) return fail(B2DP_ERR_INVALID, "plan_create: out is null");
+  *out = nullptr;
+  if (!c || !l) return fail(B2DP_ERR_INVALID, "plan_create: null context or layout");
+  if (l->nranks != c->nranks)
+    return fail(B2DP_ERR_INVALID, "plan_create: layout is cut for %d ranks, context has %d", l->nranks, c->nranks);
+  auto p = std::make_unique<b2dp_plan>();
+  p->ctx = c;
+  p->layout = *l;
+  p->map = make_map(*l);
+  for (int i = 0; i < c->nlocal; ++i) {
+    auto r = std::make_unique<RankState>();
+    r->device = c->devices[i];
+    r->rank = c->ranks[i];
+    DeviceGuard guard(r->device);
+    CUDA_TRY(cudaFree(0));  // make sure the primary context exists before driver calls
+    CUDA_TRY(cudaDeviceGetAttribute(&r->num_sms, cudaDevAttrMultiProcessorCount, r->device));
+    int rc = vmm_alloc(r->device, p->map.end, c->devices, c->nlocal, &r->own);
+    if (rc) {
+      for (auto& q : p->rs) destroy_rank(*q);
+      return rc;
+    }
+    CUDA_TRY(cudaMemset(reinterpret_cast<void*>(r->own.va), 0, p->map.end));
+    if (!l->tiles.empty()) {
+      CUDA_TRY(cudaMalloc(&r->d_tiles, sizeof(Tile) * l->tiles.size()));
+      CUDA_TRY(cudaMemcpy(r->d_tiles, l->tiles.data(), sizeof(Tile) * l->tiles.size(), cudaMemcpyHostToDevice));
+    }
+    r->base[r->rank] = reinterpret_cast<char*>(r->own.va);
+    r->attached[r->rank] = true;
+    p->rs.push_back(std::move(r));
+  }
+  if (c->local) {  // one address space: every rank sees every block at the same address
+    for (auto& r : p->rs)
+      for (auto& q : p->rs) {
+        r->base[q->rank] = reinterpret_cast<char*>(q->own.va);
+        r->attached[q->rank] = true;
+      }
+  }
+  *out = p.release();
+  return B2DP_OK;
+}
+
+extern "C" void b2dp_plan_destroy(b2dp_plan* p) {
+  if (!p) return;
+  for (auto& r : p->rs) destroy_rank(*r);
+  delete p;
+}
+
+extern "C" int b2dp_plan_export_fd(b2dp_plan* p, int* fd_out) {
+  if (!p || !fd_out) return fail(B2DP_ERR_INVALID, "export_fd: null argument");
+  if (p->ctx->local) return fail(B2DP_ERR_STATE, "export_fd: a local context maps its peers itself");
+  return vmm_export_fd(p->rs[0]->own, fd_out);
+}
+
+extern "C" int b2dp_plan_attach_peer(b2dp_plan* p, int32_t peer, int fd) {
+  if (!p) return fail(B2DP_ERR_INVALID, "attach_peer: plan is null");
+  if (p->ctx->local) return fail(B2DP_ERR_STATE, "attach_peer: a local context maps its peers itself");
+  RankState& r = *p->rs[0];
+  if (peer < 0 || peer >= p->ctx->nranks) return fail(B2DP_ERR_INVALID, "attach_peer: rank %d out of range", peer);
+  if (peer == r.rank) return B2DP_OK;
+  if (r.attached[peer]) return fail(B2DP_ERR_STATE, "attach_peer: rank %d is already attached", peer);
+  DeviceGuard guard(r.device);
+  if (int rc = vmm_import_fd(fd, p->map.end, r.device, &r.imported[peer])) return rc;
+  r.base[peer] = reinterpret_cast<char*>(r.imported[peer].va);
+  r.attached[peer] = true;
+  return B2DP_OK;
+}
+
+extern "C" int32_t b2dp_plan_ready(const b2dp_plan* p) {
+  if (!p) return 0;
+  for (auto& r : p->rs)
+    for (int i = 0; i < p->ctx->nranks; ++i)
+      if (!r->attached[i]) return 0;
+  return 1;
+}
+
+extern "C" int b2dp_plan_buffer(b2dp_plan* p, int32_t dev, int32_t which, void** ptr, int64_t* elems) {
+  RankState* r = nullptr;
+  if (int rc = get_rank(p, dev, &r)) return rc;
+  size_t off;
+  int64_t n;
+  switch (which) {
+    case B2DP_BUF_GRADS: off = p->map.grads; n = p->layout.total; break;
+    case B2DP_BUF_WEIGHTS: off = p->map.weights; n = p->layout.total; break;
+    case B2DP_BUF_REDUCED: off = p->map.reduced; n = p->layout.total; break;
+    case B2DP_BUF_STATE0: off = p->map.s0; n = p->layout.shard; break;
+    case B2DP_BUF_STATE1: off = p->map.s1; n = p->layout.shard; break;
+    case B2DP_BUF_STATS: off = p->map.ctrl + kCtrlStats; n = 4; break;
+    default: return fail(B2DP_ERR_INVALID, "plan_buffer: unknown buffer %d", which);
+  }
+  if (ptr) *ptr = r->base[r->rank] + off;
+  if (elems) *elems = n;
+  return B2DP_OK;
+}
+
+extern "C" int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream) {
+  RankState* r = nullptr;
+  if (int rc = get_rank(p, dev, &r)) return rc;
+  DeviceGuard guard(r->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int32_t st = 0;
+  void* word = r->base[r->rank] + p->map.ctrl + kCtrlStatus;
+  CUDA_TRY(cudaMemcpyAsync(&st, word, sizeof st, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  if (st != 0) {
+    CUDA_TRY(cudaMemsetAsync(word, 0, sizeof st, s));
+    return fail(st, "rank %d: a cross-GPU flag wait timed out (a peer never reached the collective)", r->rank);
+  }
+  return B2DP_OK;
+}
+
+// ------------------------------------------------------------------------- the hot path
+extern "C" int b2dp_pack(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads,
+                         int32_t grad_dtype, float prescale, void* stream) {
+  RankState* r = nullptr;
+  if (int rc = get_rank(p, dev, &r)) return rc;
+  if (grad_dtype != B2DP_F32) return fail(B2DP_ERR_INVALID, "pack: gradients must be f32 (got dtype %d)", grad_dtype);
+  DeviceGuard guard(r->device);
+  return launch_pack<0>(p, *r, bucket, r->grads, grads, p->map.grads, p->layout.wire, prescale,
+                        (cudaStream_t)stream);
+}
+
+extern "C" int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* weights, void* stream) {
+  RankState* r = nullptr;
+  if (int rc = get_rank(p, dev, &r)) return rc;
+  DeviceGuard guard(r->device);
+  return launch_pack<0>(p, *r, -1, r->weights, weights, p->map.weights, B2DP_F32, 1.0f, (cudaStream_t)stream);
+}
+
+extern "C" int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t which, void* const* outs,
+                           void* stream) {
+  RankState* r = nullptr;
+  if (int rc = get_rank(p, dev, &r)) return rc;
+  size_t off;
+  if (which == B2DP_BUF_WEIGHTS)
+    off = p->map.weights;
+  else if (which == B2DP_BUF_REDUCED)
+    off = p->map.reduced;
+  else
+    return fail(B2DP_ERR_INVALID, "unpack: buffer %d is not WEIGHTS or REDUCED", which);
+  DeviceGuard guard(r->device);
+  return launch_pack<1>(p, *r, bucket, r->outs, (const void* const*)outs, off, B2DP_F32, 1.0f,
+                        (cudaStream_t)stream);
+}
+
+extern "C" int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp_hyper* hyper,
+                         void* stream) {
+  if (opt == B2DP_OPT_NONE) return fail(B2DP_ERR_INVALID, "step: optimizer NONE -- use b2dp_allreduce");
+  return run_collective(p, dev, bucket, opt, hyper, 1.0f, 0, stream);
+}
+
+extern "C" int b2dp_reduce_scatter_apply(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt,
+                                         const b2dp_hyper* hyper, void* stream) {
+  if (opt == B2DP_OPT_NONE) return fail(B2DP_ERR_INVALID, "reduce_scatter_apply: optimizer NONE -- use b2dp_allreduce");
+  return run_collective(p, dev, bucket, opt, hyper, 1.0f, 1, stream);
+}
+
+extern "C" int b2dp_all_gather(b2dp_plan* p, int32_t dev, int32_t bucket, void* stream) {
+  return run_collective(p, dev, bucket, B2DP_OPT_NONE, nullptr, 1.0f, 3, stream);
+}
+
+extern "C" int b2dp_allreduce(b2dp_plan* p, int32_t dev, int32_t bucket, float postscale, void* stream) {
+  return run_collective(p, dev, bucket, B2DP_OPT_NONE, nullptr, postscale, 2, stream);
+}
+
+extern "C" float b2dp_adam_alpha(float lr, float beta1, float beta2, int64_t step) {
+  // fp32 scalar arithmetic, one rounding per operation (Keras computes these as fp32 tensors)
+  volatile float b1p = powf(beta1, (float)step);
+  volatile float b2p = powf(beta2, (float)step);
+  volatile float num = sqrtf(1.0f - b2p);
+  volatile float den = 1.0f - b1p;
+  volatile float a = lr * num;
+  return a / den;
+}

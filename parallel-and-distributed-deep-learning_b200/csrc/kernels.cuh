@@ -1,0 +1,369 @@
+// kernels.cuh -- the sm_100a device code of the data-parallel hot path.
+//
+// Nothing on this path is a contraction, so there are no tensor-core instructions here:
+// every kernel is a stream over HBM and/or NVLink, built from 128-bit coalesced accesses,
+// enough independent requests in flight per SM to cover HBM (~1 us) and NVLink (~2 us)
+// latency, and grids sized from the SM count.  All optimizer arithmetic uses the
+// round-to-nearest intrinsics (__fadd_rn, __fmul_rn, ...) so ptxas cannot contract a
+// multiply into an add: one rounding per operation is the contract that makes the
+// result bit-identical to the CPU oracle (TensorFlow's Eigen CPU kernels).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "internal.h"
+
+namespace b2dp {
+
+constexpr int kMaxBlocks = 1024;       // flag slots per phase; collective grids never exceed it
+constexpr int kStepThreads = 512;
+constexpr int kPackThreads = 256;
+
+// ---- memory helpers -----------------------------------------------------------------
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint2 ld_stream_u2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_f4(float4* p, float4 v) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ float4 bf16x4_to_f4(uint2 u) {
+  return make_float4(bf16lo(u.x), bf16hi(u.x), bf16lo(u.y), bf16hi(u.y));
+}
+// RNE fp32 -> bf16 (cvt.rn.bf16.f32), packed two per word
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ---- kernel (1): pack / unpack --------------------------------------------------------
+// One launch over the device-resident tile table; a tile is a run of <= 4096 elements
+// inside one tensor, so blocks are balanced by bytes however ragged the tensor list is.
+// DIR 0: tensors -> flat (cast to WireT, times prescale); DIR 1: flat(f32) -> tensors.
+template <typename WireT, int DIR>
+__global__ void __launch_bounds__(kPackThreads)
+pack_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
+            WireT* __restrict__ flat, float prescale) {
+  constexpr int V = kTileElems / (4 * kPackThreads);  // float4 per thread per tile = 4
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const Tile tl = tiles[t];
+    float* tens = reinterpret_cast<float*>(ptrs[tl.tensor]) + tl.src_off;
+    WireT* fl = flat + tl.dst_off;
+    const uint32_t count = tl.count;
+    const bool vec = ((reinterpret_cast<uintptr_t>(tens) & 15) == 0);
+    const uint32_t nvec = vec ? (count >> 2) : 0;
+    if (DIR == 0) {
+      float4 v[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        uint32_t q = j * kPackThreads + threadIdx.x;
+        if (q < nvec) v[j] = ld_stream_f4(reinterpret_cast<const float4*>(tens) + q);
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        uint32_t q = j * kPackThreads + threadIdx.x;
+        if (q < nvec) {
+          float4 x = v[j];
+          x.x = __fmul_rn(x.x, prescale);
+          x.y = __fmul_rn(x.y, prescale);
+          x.z = __fmul_rn(x.z, prescale);
+          x.w = __fmul_rn(x.w, prescale);
+          if (sizeof(WireT) == 4) {
+            st_f4(reinterpret_cast<float4*>(fl) + q, x);
+          } else {
+            uint2 o = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
+            reinterpret_cast<uint2*>(fl)[q] = o;
+          }
+        }
+      }
+      for (uint32_t i = nvec * 4 + threadIdx.x; i < count; i += kPackThreads) {
+        float x = __fmul_rn(tens[i], prescale);
+        if (sizeof(WireT) == 4)
+          reinterpret_cast<float*>(fl)[i] = x;
+        else
+          reinterpret_cast<__nv_bfloat16*>(fl)[i] = __float2bfloat16_rn(x);
+      }
+    } else {
+      const float* src = reinterpret_cast<const float*>(fl);
+      float4 v[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        uint32_t q = j * kPackThreads + threadIdx.x;
+        if (q < nvec) v[j] = ld_stream_f4(reinterpret_cast<const float4*>(src) + q);
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        uint32_t q = j * kPackThreads + threadIdx.x;
+        if (q < nvec) st_f4(reinterpret_cast<float4*>(tens) + q, v[j]);
+      }
+      for (uint32_t i = nvec * 4 + threadIdx.x; i < count; i += kPackThreads) tens[i] = src[i];
+    }
+  }
+}
+
+// ---- cross-GPU flag barrier -----------------------------------------------------------
+// Block b of every rank meets block b of every other rank: thread t < n publishes this
+// rank's epoch into rank t's flag word and waits for rank t's epoch in its own.  Epochs
+// only grow, so flags are never reset.  All ranks launch the same grid (a function of the
+// slice length and the SM count) and the grid never exceeds what is co-resident, so a
+// waiting block can never keep the block it waits for off an SM.
+struct Comm {
+  uint32_t* flags[kMaxRanks];  // flag block of every rank, as mapped on this GPU
+  int32_t* status;             // this rank's status word
+  uint64_t timeout_ns;
+  uint32_t epoch;
+  int32_t rank;
+  int32_t n;
+  int32_t use_flags;           // 0: emulated ranks or n == 1 (stream order is the barrier)
+};
+
+__device__ __forceinline__ void flag_barrier(const Comm& c, int phase) {
+  if (c.use_flags) {
+    __syncthreads();  // every thread's earlier stores are ordered before the release below
+    if (threadIdx.x < (unsigned)c.n) {
+      const int peer = threadIdx.x;
+      const size_t slot = (size_t)(phase * kMaxBlocks + blockIdx.x) * kMaxRanks;
+      st_release_sys(c.flags[peer] + slot + c.rank, c.epoch);
+      const uint32_t* mine = c.flags[c.rank] + slot + peer;
+      const uint64_t t0 = global_timer_ns();
+      uint32_t spins = 0;
+      while ((int32_t)(ld_acquire_sys(mine) - c.epoch) < 0) {
+        if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > c.timeout_ns) {
+          atomicExch(c.status, (int32_t)B2DP_ERR_TIMEOUT);
+          break;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- kernels (2)+(3): reduce-scatter(SUM) -> optimizer -> all-gather --------------------
+struct OptScalars {
+  float alpha, omb1, omb2, eps;   // Adam: alpha = lr*sqrt(1-b2^t)/(1-b1^t)
+  float lr, mu, wd;               // SGD-momentum
+  int32_t nesterov;
+  float postscale;
+};
+
+struct StepArgs {
+  const void* g[kMaxRanks];  // slice `rank` of the bucket inside every rank's wire buffer
+  float* out[kMaxRanks];     // slice `rank` of the bucket inside every rank's weight (or reduced) buffer
+  float* w;                  // = out[rank]
+  float* s0;                 // Adam m / SGD accumulator, this rank's shard of the bucket
+  float* s1;                 // Adam v
+  int64_t nvec;              // slice length in 4-element vectors
+  OptScalars o;
+  Comm c;
+  double* partials;          // scratch: 2 doubles per block
+  uint32_t* ticket;          // scratch: arrival counter of the statistics reduction
+  double* stats;             // out: [0] sum g^2, [1] non-finite count
+  int32_t want_stats;
+  int32_t push;              // 1: store results to every rank (all-gather); 0: own copy only
+};
+
+__device__ __forceinline__ void adam_update(float g, float& w, float& m, float& v, const OptScalars& o) {
+  float d1 = __fsub_rn(g, m);
+  m = __fadd_rn(m, __fmul_rn(d1, o.omb1));
+  float d2 = __fsub_rn(__fmul_rn(g, g), v);
+  v = __fadd_rn(v, __fmul_rn(d2, o.omb2));
+  float num = __fmul_rn(o.alpha, m);
+  float den = __fadd_rn(__fsqrt_rn(v), o.eps);
+  w = __fsub_rn(w, __fdiv_rn(num, den));
+}
+
+__device__ __forceinline__ void sgdm_update(float g, float& w, float& a, const OptScalars& o) {
+  if (o.wd != 0.0f) w = __fsub_rn(w, __fmul_rn(__fmul_rn(w, o.wd), o.lr));
+  float lg = __fmul_rn(o.lr, g);
+  if (o.mu != 0.0f) {
+    a = __fsub_rn(__fmul_rn(o.mu, a), lg);
+    w = o.nesterov ? __fadd_rn(w, __fsub_rn(__fmul_rn(o.mu, a), lg)) : __fadd_rn(w, a);
+  } else {
+    w = __fsub_rn(w, lg);
+  }
+}
+
+template <typename WireT>
+__device__ __forceinline__ float4 load_wire(const void* base, int64_t q) {
+  if (sizeof(WireT) == 4) return ld_stream_f4(reinterpret_cast<const float4*>(base) + q);
+  return bf16x4_to_f4(ld_stream_u2(reinterpret_cast<const uint2*>(base) + q));
+}
+
+// Deterministic block + grid reduction of the optional statistics: warp shuffles, one
+// partial per block in scratch, and the last block to arrive folds the partials in block
+// order (so the result does not depend on which block finishes first).
+__device__ __forceinline__ void stats_reduce(const StepArgs& a, double sumsq, double bad) {
+  __shared__ double sm[2][kStepThreads / 32];
+  __shared__ bool last;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
+    bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    sm[0][warp] = sumsq;
+    sm[1][warp] = bad;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    double s = lane < (int)(blockDim.x >> 5) ? sm[0][lane] : 0.0;
+    double b = lane < (int)(blockDim.x >> 5) ? sm[1][lane] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if (lane == 0) {
+      a.partials[2 * blockIdx.x] = s;
+      a.partials[2 * blockIdx.x + 1] = b;
+      __threadfence();
+      last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (last && warp == 0) {
+    __threadfence();
+    double s = 0.0, b = 0.0;
+    for (unsigned i = lane; i < gridDim.x; i += 32) {
+      s += __ldcg(a.partials + 2 * i);
+      b += __ldcg(a.partials + 2 * i + 1);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if (lane == 0) {
+      a.stats[0] = s;
+      a.stats[1] = b;
+      *a.ticket = 0;
+    }
+  }
+}
+
+// N = ranks (compile-time so the N peer loads of a vector are issued back to back);
+// OPT = b2dp_opt; U = vectors in flight per thread.
+template <int N, typename WireT, int OPT, int U>
+__global__ void __launch_bounds__(kStepThreads)
+step_kernel(const StepArgs a) {
+  flag_barrier(a.c, 0);  // every rank's bucket is packed; every rank may be written
+
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float sumsq = 0.0f;
+  float bad = 0.0f;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < a.nvec; base += stride * U) {
+    float4 g[U][N];
+    float4 w[U], s0[U], s1[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < a.nvec) {
+#pragma unroll
+        for (int r = 0; r < N; ++r) g[u][r] = load_wire<WireT>(a.g[r], q);
+        if (OPT != B2DP_OPT_NONE) {
+          w[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q);
+          s0[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.s0) + q);
+          if (OPT == B2DP_OPT_ADAM) s1[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.s1) + q);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < a.nvec) {
+        // rank-order sum: ((g0 + g1) + g2) + ... one rounding per add (TF AddN order)
+        float4 acc = g[u][0];
+#pragma unroll
+        for (int r = 1; r < N; ++r) {
+          acc.x = __fadd_rn(acc.x, g[u][r].x);
+          acc.y = __fadd_rn(acc.y, g[u][r].y);
+          acc.z = __fadd_rn(acc.z, g[u][r].z);
+          acc.w = __fadd_rn(acc.w, g[u][r].w);
+        }
+        acc.x = __fmul_rn(acc.x, a.o.postscale);
+        acc.y = __fmul_rn(acc.y, a.o.postscale);
+        acc.z = __fmul_rn(acc.z, a.o.postscale);
+        acc.w = __fmul_rn(acc.w, a.o.postscale);
+        if (a.want_stats) {
+          sumsq = fmaf(acc.x, acc.x, fmaf(acc.y, acc.y, fmaf(acc.z, acc.z, fmaf(acc.w, acc.w, sumsq))));
+          bad += (float)(!isfinite(acc.x)) + (float)(!isfinite(acc.y)) + (float)(!isfinite(acc.z)) +
+                 (float)(!isfinite(acc.w));
+        }
+        float4 res;
+        if (OPT == B2DP_OPT_ADAM) {
+          adam_update(acc.x, w[u].x, s0[u].x, s1[u].x, a.o);
+          adam_update(acc.y, w[u].y, s0[u].y, s1[u].y, a.o);
+          adam_update(acc.z, w[u].z, s0[u].z, s1[u].z, a.o);
+          adam_update(acc.w, w[u].w, s0[u].w, s1[u].w, a.o);
+          st_f4(reinterpret_cast<float4*>(a.s0) + q, s0[u]);
+          st_f4(reinterpret_cast<float4*>(a.s1) + q, s1[u]);
+          res = w[u];
+        } else if (OPT == B2DP_OPT_SGDM) {
+          sgdm_update(acc.x, w[u].x, s0[u].x, a.o);
+          sgdm_update(acc.y, w[u].y, s0[u].y, a.o);
+          sgdm_update(acc.z, w[u].z, s0[u].z, a.o);
+          sgdm_update(acc.w, w[u].w, s0[u].w, a.o);
+          if (a.o.mu != 0.0f) st_f4(reinterpret_cast<float4*>(a.s0) + q, s0[u]);
+          res = w[u];
+        } else {
+          res = acc;
+        }
+        if (N > 1 && a.push) {
+#pragma unroll
+          for (int r = 0; r < N; ++r) st_f4(reinterpret_cast<float4*>(a.out[r]) + q, res);
+        } else {
+          st_f4(reinterpret_cast<float4*>(a.w) + q, res);
+        }
+      }
+    }
+  }
+  if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
+
+  flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
+}
+
+// all-gather alone: push this rank's weight slice into every rank's weight buffer
+// (the PS "pull" of imagenet-resnet50-ps.py:75-82 when the step is run as two launches).
+template <int N>
+__global__ void __launch_bounds__(kStepThreads)
+gather_kernel(const StepArgs a) {
+  flag_barrier(a.c, 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride) {
+    float4 v = ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q);
+#pragma unroll
+    for (int r = 0; r < N; ++r)
+      if (r != a.c.rank) st_f4(reinterpret_cast<float4*>(a.out[r]) + q, v);
+  }
+  flag_barrier(a.c, 1);
+}
+
+}  // namespace b2dp
