@@ -1,0 +1,444 @@
+#!/usr/bin/env python
+"""bench.py -- ResNet-50 data-parallel training throughput with the B200-native hot path.
+
+Metric (BASELINE.json): ResNet-50 images/sec at 1/2/4/8 B200, with the per-step gradient
+all-reduce + optimizer apply (the hot path) going through libb200dp.so; the same line also
+carries the hot path's own time, its all-reduce bus bandwidth and the roofline of its
+dominant kernel.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            one JSON line
+  torchrun ... bench.py --gpus N ...                              one rank per GPU
+  python bench.py --impl reference ...                            CPU restatement arm
+  python bench.py --hotpath-only ...                              skip the conv graph (ncu runs)
+
+A step = forward/backward of the Keras-shaped ResNet-50 on one synthetic batch (stand-in
+torch/cuDNN graph: TensorFlow is absent on this image) + pack + fused
+reduce-scatter/Adam/all-gather.  `value` has the batch resident in HBM; `e2e` copies every
+step's batch from pinned host memory and reads the loss back, inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "resnet50_train_images_per_sec"
+UNIT = "images/s"
+N_ELEMS = 25_583_592          # Keras ResNet-50 trainable elements
+NVLINK_PEAK_GBS = 770.0       # measured peer copy per direction (B200_PROFILING.md); 900 nominal
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200dp", choices=["b200dp", "reference"])
+    ap.add_argument("--batch", type=int, default=256, help="images per GPU (BASELINE.json configs[1])")
+    ap.add_argument("--optimizer", default="adam", choices=["adam", "sgdm"])
+    ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--hotpath-only", action="store_true", help="time only pack+step on synthetic gradients")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-batch", type=int, default=32, help="CPU arm: images per step (configs[0])")
+    return ap.parse_args()
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.path = gpu_index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            try:
+                self.proc.kill()
+            except Exception:
+                pass
+        try:
+            sm, reasons, mx = [], set(), None
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx = float(f[2])
+                except ValueError:
+                    continue
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                     f[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+            if sm:
+                sm.sort()
+                out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+        except Exception:
+            pass
+        return out
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def cpu_training_step_baseline(n_replicas, batch, steps, warmup, budget_s=150.0):
+    """The reference's CPU path restated: Keras-shaped ResNet-50 forward/backward on the host
+    cores (torch CPU; TensorFlow is absent), then the oracle's replica-order AddN over
+    n_replicas gradient copies and TF-form Adam over all 25.58M elements.  One replica's
+    batch is computed per step (a bounded sample: MirroredStrategy on CPU runs its replicas
+    on the same cores, so images/s does not grow with the replica count)."""
+    import numpy as np
+    import torch
+    import oracle
+    from b200dp import harness
+    cores = host_cores()
+    torch.set_num_threads(cores)
+    oracle.set_threads(cores)
+    model = harness.KerasResNet50().train()
+    params = model.keras_order_params()
+    g = torch.Generator().manual_seed(7)
+    x = torch.rand(batch, 3, 224, 224, generator=g) * 255.0
+    y = torch.randint(0, 1000, (batch,), generator=g)
+    N = sum(p.numel() for p in params)
+    w = np.concatenate([p.detach().numpy().ravel() for p in params]).astype(np.float32)
+    m, v = np.zeros(N, np.float32), np.zeros(N, np.float32)
+    others = [np.random.default_rng(r).standard_normal(N).astype(np.float32) * 1e-3 for r in range(1, n_replicas)]
+    gsum = np.empty(N, np.float32)
+    times, hot = [], []
+    for it in range(warmup + steps):
+        if it == 1 and budget_s and first_dt * (warmup + steps) > budget_s and batch > 4:
+            # bounded sample: shrink the batch so the whole run fits the time budget
+            while batch > 4 and first_dt * (warmup + steps) > budget_s:
+                batch //= 2
+                first_dt /= 2
+            x, y = x[:batch], y[:batch]
+        t0 = time.perf_counter()
+        for p in params:
+            p.grad = None
+        loss = torch.nn.functional.cross_entropy(model(x), y) / n_replicas
+        loss.backward()
+        g0 = np.concatenate([p.grad.numpy().ravel() for p in params])
+        t1 = time.perf_counter()
+        oracle.addn([g0] + others, out=gsum)
+        oracle.adam_(w, m, v, gsum, lr=1e-3, step=it + 1)
+        t2 = time.perf_counter()
+        o = 0
+        with torch.no_grad():
+            for p in params:
+                p.copy_(torch.from_numpy(w[o:o + p.numel()]).view(p.shape))
+                o += p.numel()
+        t3 = time.perf_counter()
+        if it == 0:
+            first_dt = t3 - t0
+        if it >= warmup:
+            times.append(t3 - t0)
+            hot.append(t2 - t1)
+    dt = sum(times) / len(times)
+    return {"images_per_s": batch / dt, "ms_per_step": dt * 1e3, "hot_path_ms": sum(hot) / len(hot) * 1e3,
+            "cores": cores, "loss": float(loss.detach()), "batch": batch}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = cpu_training_step_baseline(args.gpus, args.ref_batch, max(1, args.steps), max(1, args.warmup))
+    args.ref_batch = r["batch"]
+    sample = ("%d steps of one replica's batch %d (configs[0]) fwd+bwd on torch-CPU + oracle AddN over %d "
+              "replica gradients + TF-form Adam over all 25,583,592 elements; port of the reference's CPU path, "
+              "TensorFlow itself is not installable here" % (args.steps, args.ref_batch, args.gpus))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["images_per_s"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, args.gpus, cpu=True),
+        "cpu_baseline": {"value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": sample, "hot_path_ms": r["hot_path_ms"]},
+        "e2e": {"value": r["images_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, n, cpu=False):
+    return {
+        "workload": "imagenet-resnet50-mirror.py: Keras ResNet-50 (214 tensors, 25,583,592 params), synthetic "
+                    "224x224x3, batch %d/GPU, Adam; gradient SUM + optimizer apply via b200dp" % args.batch,
+        "global_batch": (args.ref_batch if cpu else args.batch * n), "per_gpu_batch": args.ref_batch if cpu else args.batch,
+        "optimizer": args.optimizer, "wire_dtype": args.wire, "parallelism": "dp%d" % n,
+        "conv_graph": "torch-CPU stand-in" if cpu else "torch+cuDNN stand-in (TF32 convs, as TF defaults)",
+        "l2": "inputs_exceed_l2 (activations and 409 MB of w/m/v/g per step >> 126 MB L2)",
+    }
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_b200dp(args):
+    import torch
+    import torch.distributed as dist
+    import b200dp
+    from b200dp import harness
+
+    n = args.gpus
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != n:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N>1 with torch.distributed.run, one rank per GPU" % (n, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200; the library has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if n > 1:
+        dist.init_process_group("nccl", device_id=device)
+    torch.backends.cudnn.benchmark = True
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+
+    numels = b200dp.resnet50_numels()
+    ctx = b200dp.Context.rank(rank, n, local_rank)
+    lay = b200dp.Layout(numels, nranks=n, wire=args.wire)
+    plan = b200dp.Plan(ctx, lay)
+    if n > 1:
+        session = "bench-%s-%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
+        obj = [session]
+        dist.broadcast_object_list(obj, src=0)
+        plan.exchange(obj[0])
+        dist.barrier()
+
+    B = args.batch
+    gen = torch.Generator(device=device).manual_seed(7 + rank)
+    host_gen = torch.Generator().manual_seed(7 + rank)
+    launches_per_step = 2  # pack + fused step
+
+    if args.hotpath_only:
+        flat_g = torch.randn(sum(numels), generator=gen, device=device) * 1e-3
+        grads, o = [], 0
+        for k in numels:
+            grads.append(flat_g[o:o + k])
+            o += k
+        plan.tensor(0, b200dp.BUF_WEIGHTS).uniform_(-0.05, 0.05)
+        t = [0]
+
+        def hot():
+            t[0] += 1
+            plan.pack(0, grads)
+            plan.step(0, args.optimizer, b200dp.adam_hyper(step=t[0]) if args.optimizer == "adam"
+                      else b200dp.sgdm_hyper())
+
+        def step_resident():
+            hot()
+            return None
+
+        step_e2e = None
+        stepper = None
+    else:
+        model = harness.KerasResNet50().to(device).to(memory_format=torch.channels_last).train()
+        stepper = harness.DataParallelStep(model, plan, dev=0, optimizer=args.optimizer, lr=1e-3)
+        x_dev = (torch.rand(B, 3, 224, 224, generator=gen, device=device) * 255.0).contiguous(
+            memory_format=torch.channels_last)
+        y_dev = torch.randint(0, 1000, (B,), generator=gen, device=device)
+        # host batch as tf.data hands it over: float32 NHWC (the scripts cast to float32, -mirror.py:49)
+        x_host = (torch.rand(B, 224, 224, 3, generator=host_gen) * 255.0).pin_memory()
+        y_host = torch.randint(0, 1000, (B,), generator=host_gen).pin_memory()
+        x_stage = torch.empty(B, 224, 224, 3, device=device)
+        loss_host = torch.empty((), pin_memory=True)
+
+        def step_resident():
+            return stepper(x_dev, y_dev)
+
+        def step_e2e():
+            x_stage.copy_(x_host, non_blocking=True)
+            y = y_host.to(device, non_blocking=True)
+            loss = stepper(x_stage.permute(0, 3, 1, 2), y)   # NHWC memory viewed as channels_last NCHW
+            loss_host.copy_(loss.detach(), non_blocking=True)
+            torch.cuda.current_stream().synchronize()          # the user reads the loss every step
+            return loss_host
+
+        hot = stepper.hot_path
+
+    def barrier():
+        if n > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, hot_events=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        if n > 1:
+            tms = torch.tensor([ms], device=device)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = float(tms.item())
+        return ms / steps
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_step = timed(step_resident, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # the hot path alone, and its dominant kernel alone, timed with events on the launch stream
+    # (warm caches are not an issue: 409 MB of w/m/v/g per rank per step >> L2)
+    def time_region(fn, reps):
+        barrier()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        torch.cuda._sleep(int(2e7))   # ~10 ms: lets the host queue every launch, so events time the GPU only
+        e[0].record()
+        for i in range(reps):
+            fn()
+            e[i + 1].record()
+        barrier()
+        ts = sorted(e[i].elapsed_time(e[i + 1]) for i in range(reps))
+        t = torch.tensor([ts[len(ts) // 2], sum(ts) / len(ts)], device=device)
+        if n > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1])
+
+    grads_for_pack = b200dp.ptr_array(grads if args.hotpath_only else [p.grad for p in stepper.params])
+    tcount = [10 ** 6]
+
+    def only_step():
+        tcount[0] += 1
+        h = b200dp.adam_hyper(step=tcount[0]) if args.optimizer == "adam" else b200dp.sgdm_hyper()
+        plan.step(0, args.optimizer, h)
+
+    def only_pack():
+        plan.pack(0, grads_for_pack)
+
+    def pack_and_step():
+        only_pack()
+        only_step()
+
+    reps = 30
+    for _ in range(5):
+        pack_and_step()
+    hot_med_ms, hot_avg_ms = time_region(pack_and_step, reps)
+    step_med_ms, step_avg_ms = time_region(only_step, reps)
+    pack_med_ms, pack_avg_ms = time_region(only_pack, reps)
+    plan.check(0)
+
+    e2e = None
+    if step_e2e is not None:
+        ms_e2e = timed(step_e2e, args.steps, args.warmup)
+        e2e = {"value": n * B / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": n * (x_host.numel() * 4 + y_host.numel() * 8), "d2h_bytes_per_step": n * 4}
+
+    if rank != 0:
+        if n > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    peaks, peak_kind = measured_peaks()
+    elems_per_rank = lay.shard_elems          # padded slice; algorithmic bytes use the unpadded N/n
+    S = 4 * N_ELEMS
+    if n == 1:
+        bytes_per_elem = 28 if args.optimizer == "adam" else 20
+        alg_bytes = bytes_per_elem * N_ELEMS
+        achieved = alg_bytes / (step_avg_ms * 1e-3) / 1e9
+        roofline = {"kernel": "step_kernel<N=1,%s,%s> (fused optimizer apply)" % (args.wire, args.optimizer),
+                    "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "frac": achieved / peaks["hbm_gbs"], "peak_source": peak_kind + " (MEASURED_PEAKS.json copy bandwidth)",
+                    "algorithmic_bytes_per_launch": alg_bytes, "us_per_launch": step_avg_ms * 1e3,
+                    "traffic": load_traffic("step_n1")}
+    else:
+        wire_b = 2 if args.wire == "bf16" else 4
+        nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S   # per GPU per direction: RS reads in + AG writes in
+        achieved = nvl_bytes / (step_avg_ms * 1e-3) / 1e9
+        roofline = {"kernel": "step_kernel<N=%d,%s,%s> (reduce-scatter + apply + all-gather over NVLink peer memory)"
+                              % (n, args.wire, args.optimizer),
+                    "bound": "nvlink", "achieved": achieved, "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
+                    "frac": achieved / NVLINK_PEAK_GBS,
+                    "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
+                    "algorithmic_bytes_per_launch": nvl_bytes, "us_per_launch": step_avg_ms * 1e3, "traffic": None}
+    busbw = (S / (step_avg_ms * 1e-3)) * 2 * (n - 1) / n / 1e9 if n > 1 else 0.0
+    hot_path = {"us_pack_plus_step_median": hot_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
+                "us_pack_kernel_avg": pack_avg_ms * 1e3, "share_of_train_step": hot_avg_ms / ms_step,
+                "allreduce_busbw_gbs": busbw, "busbw_vs_900": busbw / 900.0,
+                "pack_hbm_gbs": (4 + (2 if args.wire == "bf16" else 4)) * N_ELEMS / (pack_avg_ms * 1e-3) / 1e9,
+                "elems_per_rank": elems_per_rank}
+
+    line = {
+        "metric": METRIC if not args.hotpath_only else "hot_path_steps_per_sec_as_images",
+        "value": n * B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
+        "clocks": clocks, "gpu_launches": launches_per_step * args.steps,
+        "gpu_launches_note": "pack_kernel + step_kernel per step (libb200dp.so); conv graph launches are torch/cuDNN's",
+        "roofline": roofline, "hot_path": hot_path,
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if n == 1 and not args.no_cpu_baseline and not args.hotpath_only:
+        r = cpu_training_step_baseline(1, args.ref_batch, 3, 1)
+        line["cpu_baseline"] = {
+            "value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+            "sample": "3 steps (1 warm-up) of batch %d (configs[0]) fwd+bwd on torch-CPU + oracle TF-form Adam over "
+                      "25,583,592 elements" % args.ref_batch,
+            "hot_path_ms": r["hot_path_ms"]}
+    print(json.dumps(line))
+    if n > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def load_traffic(key):
+    """dram bytes (read+write) per launch from the committed ncu --set full capture, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200dp(a)

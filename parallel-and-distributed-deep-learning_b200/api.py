@@ -131,7 +131,15 @@ def _stream_handle(stream, device):
     return ctypes.c_void_p(int(stream))
 
 
+def ptr_array(tensors_or_ptrs):
+    """ctypes array of device pointers; build it once and reuse it when the tensors' addresses
+    are stable (214 data_ptr() calls cost more host time than the pack kernel takes)."""
+    return _ptr_array(tensors_or_ptrs)
+
+
 def _ptr_array(tensors_or_ptrs):
+    if isinstance(tensors_or_ptrs, ctypes.Array):
+        return tensors_or_ptrs
     vals = [int(t.data_ptr()) if hasattr(t, "data_ptr") else int(t) for t in tensors_or_ptrs]
     return (ctypes.c_void_p * max(1, len(vals)))(*vals)
 
@@ -198,39 +206,44 @@ class Plan:
         t = torch.as_tensor(_DevMem(ptr, (n,), typestr, self), device=device)
         return t.view(dt) if t.dtype != dt else t
 
+    def _stream(self, stream, dev):
+        device = self.ctx.devices[dev] if 0 <= dev < len(self.ctx.devices) else 0  # the library rejects bad dev
+        return _stream_handle(stream, device)
+
     # -- the hot path --------------------------------------------------------------------
     def pack(self, dev, grads, prescale=1.0, bucket=-1, stream=None):
-        if len(grads) != self.layout.num_tensors:
+        if len(grads) != max(1, self.layout.num_tensors) if isinstance(grads, ctypes.Array) \
+                else len(grads) != self.layout.num_tensors:
             raise ValueError("pack: %d tensors, plan has %d" % (len(grads), self.layout.num_tensors))
         check(self._L.b2dp_pack(self._h, dev, bucket, _ptr_array(grads), F32, prescale,
-                                _stream_handle(stream, self.ctx.devices[dev])))
+                                self._stream(stream, dev)))
 
     def load_weights(self, dev, weights, stream=None):
         if len(weights) != self.layout.num_tensors:
             raise ValueError("load_weights: %d tensors, plan has %d" % (len(weights), self.layout.num_tensors))
         check(self._L.b2dp_load_weights(self._h, dev, _ptr_array(weights),
-                                        _stream_handle(stream, self.ctx.devices[dev])))
+                                        self._stream(stream, dev)))
 
     def unpack(self, dev, outs, which=BUF_WEIGHTS, bucket=-1, stream=None):
         if len(outs) != self.layout.num_tensors:
             raise ValueError("unpack: %d tensors, plan has %d" % (len(outs), self.layout.num_tensors))
         check(self._L.b2dp_unpack(self._h, dev, bucket, which, _ptr_array(outs),
-                                  _stream_handle(stream, self.ctx.devices[dev])))
+                                  self._stream(stream, dev)))
 
     def step(self, dev, opt, hyper, bucket=-1, stream=None):
         check(self._L.b2dp_step(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
-                                _stream_handle(stream, self.ctx.devices[dev])))
+                                self._stream(stream, dev)))
 
     def reduce_scatter_apply(self, dev, opt, hyper, bucket=-1, stream=None):
         check(self._L.b2dp_reduce_scatter_apply(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
-                                                _stream_handle(stream, self.ctx.devices[dev])))
+                                                self._stream(stream, dev)))
 
     def all_gather(self, dev, bucket=-1, stream=None):
-        check(self._L.b2dp_all_gather(self._h, dev, bucket, _stream_handle(stream, self.ctx.devices[dev])))
+        check(self._L.b2dp_all_gather(self._h, dev, bucket, self._stream(stream, dev)))
 
     def allreduce(self, dev, postscale=1.0, bucket=-1, stream=None):
         check(self._L.b2dp_allreduce(self._h, dev, bucket, postscale,
-                                     _stream_handle(stream, self.ctx.devices[dev])))
+                                     self._stream(stream, dev)))
 
     def check(self, dev, stream=None):
-        check(self._L.b2dp_plan_check(self._h, dev, _stream_handle(stream, self.ctx.devices[dev])))
+        check(self._L.b2dp_plan_check(self._h, dev, self._stream(stream, dev)))

@@ -1,0 +1,358 @@
+"""GPU parity tests: the CUDA hot path, called through the C ABI (ctypes), against the CPU
+oracle and the committed golden vectors.  Bar: BIT-EXACT for the fp32 rank-order sum and
+for Adam / SGD-momentum state and weights (the kernels use one rounding per operation, no
+FMA contraction, like the oracle); the only tolerance in this file is the gradient-norm
+statistic (double accumulation in a different order: rel 1e-6).
+
+n > 1 on a one-GPU box runs as *emulated ranks* (every rank's buffers on cuda:0, the
+collective kernels launched rank after rank with the flag waits off), which exercises
+exactly the peer-pointer arithmetic the multi-GPU run uses."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+import b200dp  # noqa: E402
+import oracle  # noqa: E402
+
+F = np.float32
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=F).view(np.uint32)
+
+
+def split(flat, numels):
+    out, o = [], 0
+    for n in numels:
+        out.append(np.ascontiguousarray(flat[o:o + n]))
+        o += n
+    return out
+
+
+def dev(arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in arrs]
+
+
+def read_tensors(plan, r, numels, which=None):
+    outs = [torch.empty(n, device="cuda", dtype=torch.float32) for n in numels]
+    plan.unpack(r, outs, which=b200dp.BUF_WEIGHTS if which is None else which)
+    torch.cuda.synchronize()
+    return np.concatenate([o.cpu().numpy() for o in outs]) if outs else np.zeros(0, F)
+
+
+def gather_state(plan, lay, n, which, numels):
+    """Reassembles a sharded state (m / v / a) into tensor order from every rank's shard."""
+    flat = np.zeros(lay.total_elems, F)
+    for r in range(n):
+        shard = plan.tensor(r, which).cpu().numpy()
+        for b in range(lay.num_buckets):
+            info = lay.bucket_info(b)
+            lo = info["offset"] + r * info["slice"]
+            flat[lo:lo + info["slice"]] = shard[info["shard_off"]:info["shard_off"] + info["slice"]]
+    return np.concatenate([flat[lay.tensor_offset(k):lay.tensor_offset(k) + m] for k, m in enumerate(numels)]) \
+        if numels else np.zeros(0, F)
+
+
+def make_plan(numels, n, wire="f32", bucket_bytes=0):
+    ctx = b200dp.Context.local([0] * n)
+    lay = b200dp.Layout(numels, nranks=n, wire=wire, bucket_bytes=bucket_bytes)
+    return ctx, lay, b200dp.Plan(ctx, lay)
+
+
+# ------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("wire", ["f32", "bf16"])
+@pytest.mark.parametrize("bucket_bytes", [0, 4096])
+def test_golden_adam_three_steps(golden, wire, bucket_bytes):
+    numels = [int(x) for x in golden["numels"]]
+    n = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n, wire, bucket_bytes)
+    w0 = dev(split(golden["w0"], numels))
+    for r in range(n):
+        plan.load_weights(r, w0)
+    for s in range(3):
+        gts = [dev(split(golden["grads"][s, r], numels)) for r in range(n)]
+        for r in range(n):
+            plan.pack(r, gts[r])
+        for r in range(n):
+            plan.step(r, "adam", b200dp.adam_hyper(lr=float(golden["lrs"][s]), step=s + 1))
+    for r in range(n):
+        assert np.array_equal(bits(read_tensors(plan, r, numels)), bits(golden["adam_w_" + wire])), "rank %d" % r
+        plan.check(r)
+    assert np.array_equal(bits(gather_state(plan, lay, n, b200dp.BUF_STATE0, numels)), bits(golden["adam_m_" + wire]))
+    assert np.array_equal(bits(gather_state(plan, lay, n, b200dp.BUF_STATE1, numels)), bits(golden["adam_v_" + wire]))
+
+
+@pytest.mark.parametrize("wire", ["f32", "bf16"])
+def test_golden_allreduce_sum(golden, wire):
+    numels = [int(x) for x in golden["numels"]]
+    n = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n, wire)
+    for s in range(3):
+        gts = [dev(split(golden["grads"][s, r], numels)) for r in range(n)]
+        for r in range(n):
+            plan.pack(r, gts[r])
+        for r in range(n):
+            plan.allreduce(r)
+        for r in range(n):
+            got = read_tensors(plan, r, numels, b200dp.BUF_REDUCED)
+            assert np.array_equal(bits(got), bits(golden["sum_" + wire][s])), "step %d rank %d" % (s, r)
+
+
+def test_golden_hvd_average_then_adam(golden):
+    numels = [int(x) for x in golden["numels"]]
+    n = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n)
+    w0 = dev(split(golden["w0"], numels))
+    for r in range(n):
+        plan.load_weights(r, w0)
+    for s in range(3):
+        gts = [dev(split(golden["grads"][s, r], numels)) for r in range(n)]
+        for r in range(n):
+            plan.pack(r, gts[r])
+        for r in range(n):
+            plan.step(r, "adam", b200dp.adam_hyper(lr=float(golden["lrs"][s]), step=s + 1, postscale=1.0 / n))
+    assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(golden["hvdavg_adam_w_f32"]))
+
+
+@pytest.mark.parametrize("nest", [False, True])
+@pytest.mark.parametrize("wire", ["f32", "bf16"])
+def test_golden_sgdm(golden, nest, wire):
+    numels = [int(x) for x in golden["numels"]]
+    n = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n, wire)
+    w0 = dev(split(golden["w0"], numels))
+    for r in range(n):
+        plan.load_weights(r, w0)
+    for s in range(3):
+        gts = [dev(split(golden["grads"][s, r], numels)) for r in range(n)]
+        for r in range(n):
+            plan.pack(r, gts[r])
+        for r in range(n):
+            plan.step(r, "sgdm", b200dp.sgdm_hyper(lr=float(golden["sgd_lrs"][s]), momentum=0.9, nesterov=nest,
+                                                   weight_decay=1e-4))
+    tag = "sgdm_nest" if nest else "sgdm"
+    for r in range(n):
+        assert np.array_equal(bits(read_tensors(plan, r, numels)), bits(golden[tag + "_w_" + wire]))
+    assert np.array_equal(bits(gather_state(plan, lay, n, b200dp.BUF_STATE0, numels)), bits(golden[tag + "_a_" + wire]))
+
+
+# ------------------------------------------------------- full-size ResNet-50 vs oracle
+def resnet_inputs(n, seed):
+    """Synthetic per-rank gradients (SURVEY 8d D1 + D2 mix) generated on the GPU, mirrored to host."""
+    numels = b200dp.resnet50_numels()
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    flat = []
+    for r in range(n):
+        x = torch.randn(sum(numels), generator=g, device="cuda") * 1e-3
+        x[::7] += (-1.0) ** r * 1e2          # cancellation stress on every 7th element
+        flat.append(x)
+    return numels, flat
+
+
+def views(flat, numels):
+    out, o = [], 0
+    for n in numels:
+        out.append(flat[o:o + n])
+        o += n
+    return out
+
+
+@pytest.mark.parametrize("n,wire", [(1, "f32"), (2, "f32"), (8, "f32"), (8, "bf16"), (3, "f32")])
+def test_resnet50_adam_steps_bit_exact(n, wire):
+    numels, _ = resnet_inputs(0, 0)
+    N = sum(numels)
+    ctx, lay, plan = make_plan(numels, n, wire)
+    gen = torch.Generator(device="cuda").manual_seed(42)
+    w_flat = (torch.rand(N, generator=gen, device="cuda") - 0.5) * 0.1
+    for r in range(n):
+        plan.load_weights(r, views(w_flat, numels))
+    w_ref = w_flat.cpu().numpy().copy()
+    m_ref, v_ref = np.zeros(N, F), np.zeros(N, F)
+    lrs = [1e-3, 1e-3, 1e-4]
+    for s in range(3):
+        _, flats = resnet_inputs(n, 1234 + s)
+        for r in range(n):
+            plan.pack(r, views(flats[r], numels))
+        for r in range(n):
+            plan.step(r, "adam", b200dp.adam_hyper(lr=lrs[s], step=s + 1, want_stats=True))
+        host = [f.cpu().numpy() for f in flats]
+        gsum = oracle.addn(host, bf16_wire=(wire == "bf16"))
+        oracle.adam_(w_ref, m_ref, v_ref, gsum, lr=lrs[s], step=s + 1)
+        # gradient-norm statistic: per-rank partial sums of squares add up to the oracle's
+        torch.cuda.synchronize()
+        tot = sum(float(plan.tensor(r, b200dp.BUF_STATS)[0]) for r in range(n))
+        bad = sum(float(plan.tensor(r, b200dp.BUF_STATS)[1]) for r in range(n))
+        assert abs(tot - oracle.sumsq(gsum)) <= 1e-6 * oracle.sumsq(gsum)   # tolerance: rel 1e-6
+        assert bad == 0
+    for r in range(n):
+        assert np.array_equal(bits(read_tensors(plan, r, numels)), bits(w_ref)), "weights, rank %d" % r
+        plan.check(r)
+    assert np.array_equal(bits(gather_state(plan, lay, n, b200dp.BUF_STATE0, numels)), bits(m_ref))
+    assert np.array_equal(bits(gather_state(plan, lay, n, b200dp.BUF_STATE1, numels)), bits(v_ref))
+
+
+def test_resnet50_weights_alias_flat_buffer():
+    """A harness may make its variables views of B2DP_BUF_WEIGHTS (no unpack needed)."""
+    numels = b200dp.resnet50_numels()
+    ctx, lay, plan = make_plan(numels, 1)
+    wflat = plan.tensor(0, b200dp.BUF_WEIGHTS)
+    assert wflat.numel() == lay.total_elems and wflat.dtype == torch.float32
+    wflat.fill_(0.25)
+    g = torch.full((sum(numels),), 0.5, device="cuda")
+    plan.pack(0, views(g, numels))
+    plan.step(0, "sgdm", b200dp.sgdm_hyper(lr=0.5, momentum=0.0))
+    torch.cuda.synchronize()
+    k = 100
+    off = lay.tensor_offset(k)
+    assert torch.all(wflat[off:off + numels[k]] == 0.0)      # 0.25 - 0.5*0.5, exact
+
+
+# --------------------------------------------------------- properties at full size
+def test_pack_unpack_roundtrip_and_unaligned_sources():
+    """pack then unpack(GRADS==REDUCED for an f32 wire) is the identity, including tensors
+    whose device pointers are only 4-byte aligned (scalar path) and ragged sizes."""
+    rng = np.random.default_rng(5)
+    numels = [1, 3, 4099, 64, 0, 12345, 4096, 8191, 77]
+    big = torch.randn(sum(numels) + len(numels) + 8, device="cuda")
+    srcs, o = [], 1            # start at element 1: every tensor is deliberately misaligned
+    for n in numels:
+        srcs.append(big[o:o + n])
+        o += n + 1
+    ctx, lay, plan = make_plan(numels, 1)
+    plan.pack(0, srcs, prescale=1.0)
+    got = read_tensors(plan, 0, numels, b200dp.BUF_REDUCED)
+    want = np.concatenate([s.cpu().numpy() for s in srcs])
+    assert np.array_equal(bits(got), bits(want))
+    # padding between tensors stays zero
+    flat = plan.tensor(0, b200dp.BUF_GRADS).cpu().numpy()
+    mask = np.ones(lay.total_elems, bool)
+    for k, n in enumerate(numels):
+        mask[lay.tensor_offset(k):lay.tensor_offset(k) + n] = False
+    assert not flat[mask].any()
+
+
+def test_prescale_and_bf16_pack_match_oracle():
+    numels = [1000, 4096, 33]
+    x = torch.randn(sum(numels), device="cuda") * 3
+    ctx, lay, plan = make_plan(numels, 1, "bf16")
+    plan.pack(0, views(x, numels), prescale=0.125)
+    torch.cuda.synchronize()
+    flat = plan.tensor(0, b200dp.BUF_GRADS).view(torch.int16).cpu().numpy().view(np.uint16)
+    want = oracle.cast_bf16((x.cpu().numpy() * F(0.125)).astype(F))
+    o = 0
+    for k, n in enumerate(numels):
+        off = lay.tensor_offset(k)
+        assert np.array_equal(flat[off:off + n], want[o:o + n])
+        o += n
+
+
+def test_allreduce_of_identical_ranks_is_exact_multiple():
+    """Linearity: n equal inputs sum to n*g exactly when n is a power of two."""
+    numels = b200dp.resnet50_numels()
+    n = 4
+    ctx, lay, plan = make_plan(numels, n)
+    g = torch.randn(sum(numels), device="cuda")
+    for r in range(n):
+        plan.pack(r, views(g, numels))
+    for r in range(n):
+        plan.allreduce(r, postscale=1.0 / n)
+    torch.cuda.synchronize()
+    for r in range(n):
+        red = plan.tensor(r, b200dp.BUF_REDUCED)
+        for k in (0, 57, 213):
+            off = lay.tensor_offset(k)
+            assert torch.equal(red[off:off + numels[k]], views(g, numels)[k])
+
+
+def test_two_launch_form_equals_fused_step():
+    """reduce_scatter_apply + all_gather (PS push / pull) == the fused step, bit for bit."""
+    numels = [5000, 64, 70001]
+    n = 4
+    rng = np.random.default_rng(9)
+    grads = [[(rng.standard_normal(k) * 1e-2).astype(F) for k in numels] for _ in range(n)]
+    w0 = [rng.standard_normal(k).astype(F) for k in numels]
+    results = []
+    for fused in (True, False):
+        ctx, lay, plan = make_plan(numels, n)
+        for r in range(n):
+            plan.load_weights(r, dev(w0))
+            plan.pack(r, dev(grads[r]))
+        h = b200dp.adam_hyper(step=1)
+        if fused:
+            for r in range(n):
+                plan.step(r, "adam", h)
+        else:
+            for r in range(n):
+                plan.reduce_scatter_apply(r, "adam", h)
+            for r in range(n):
+                plan.all_gather(r)
+        results.append([read_tensors(plan, r, numels) for r in range(n)])
+    for r in range(n):
+        assert np.array_equal(bits(results[0][r]), bits(results[1][r]))
+        assert np.array_equal(bits(results[0][r]), bits(results[0][0]))
+
+
+def test_nonfinite_gradients_propagate_and_are_counted():
+    numels = [4096]
+    ctx, lay, plan = make_plan(numels, 2)
+    g0 = torch.ones(4096, device="cuda")
+    g1 = torch.ones(4096, device="cuda")
+    g0[5] = float("inf")
+    g1[5] = float("-inf")
+    g1[4000] = float("nan")
+    for r, g in enumerate((g0, g1)):
+        plan.load_weights(r, [torch.zeros(4096, device="cuda")])
+        plan.pack(r, [g])
+    for r in range(2):
+        plan.step(r, "adam", b200dp.adam_hyper(step=1, want_stats=True))
+    torch.cuda.synchronize()
+    bad = sum(float(plan.tensor(r, b200dp.BUF_STATS)[1]) for r in range(2))
+    assert bad == 2
+    w = read_tensors(plan, 0, numels)
+    assert np.isnan(w[5]) and np.isnan(w[4000]) and np.isfinite(w[6])
+
+
+def test_empty_and_all_empty_plans():
+    for numels in ([], [0, 0]):
+        ctx, lay, plan = make_plan(numels, 2)
+        ts = [torch.empty(0, device="cuda") for _ in numels]
+        for r in range(2):
+            plan.pack(r, ts)
+        for r in range(2):
+            plan.step(r, "adam", b200dp.adam_hyper(step=1))
+            plan.allreduce(r)
+            plan.check(r)
+
+
+def test_argument_errors():
+    ctx, lay, plan = make_plan([128, 128], 1)
+    with pytest.raises(ValueError):
+        plan.pack(0, [torch.zeros(128, device="cuda")])          # wrong tensor count
+    with pytest.raises(b200dp.B200dpError):
+        plan.step(0, "none", b200dp.adam_hyper())                 # NONE is allreduce's job
+    with pytest.raises(b200dp.B200dpError):
+        plan.step(0, "adam", b200dp.adam_hyper(step=0))           # Adam step is 1-based
+    with pytest.raises(b200dp.B200dpError):
+        plan.step(1, "adam", b200dp.adam_hyper())                 # no such local rank
+    with pytest.raises(b200dp.B200dpError):
+        plan.step(0, "adam", b200dp.adam_hyper(), bucket=3)       # no such bucket
+    lay8 = b200dp.Layout([128], nranks=8)
+    with pytest.raises(b200dp.B200dpError):
+        b200dp.Plan(ctx, lay8)                                    # layout cut for another rank count
+
+
+def test_lr_is_a_per_call_argument():
+    """The scripts' callbacks change lr while training (ReduceLROnPlateau, warm-up)."""
+    numels = [2048]
+    ctx, lay, plan = make_plan(numels, 1)
+    w = np.ones(2048, F)
+    plan.load_weights(0, dev([w]))
+    w_ref, m, v = w.copy(), np.zeros(2048, F), np.zeros(2048, F)
+    g = (np.arange(2048, dtype=F) - 1000) * F(1e-3)
+    for step, lr in enumerate([0.8, 0.08, 1e-5], start=1):
+        plan.pack(0, dev([g]))
+        plan.step(0, "adam", b200dp.adam_hyper(lr=lr, step=step))
+        oracle.adam_(w_ref, m, v, g, lr=lr, step=step)
+    assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(w_ref))

@@ -25,8 +25,7 @@ def _fd_worker(rank, n, session, q):
     got = {}
     if rc == 0:
         for r in range(n):
-            os.lseek(fds[r], 0, os.SEEK_SET)
-            got[r] = os.read(fds[r], 64).decode()
+            got[r] = os.pread(fds[r], 64, 0).decode()   # pread: the open file description is shared
     q.put((rank, rc, got, L.b2dp_last_error().decode()))
 
 
