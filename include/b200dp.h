@@ -198,6 +198,30 @@ int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* weights, voi
  * so a checker can use the library's exact value. */
 float b2dp_adam_alpha(float lr, float beta1, float beta2, int64_t step);
 
+/* ------------------------------------------------- entry point that allocates nothing --
+ * No counterpart in the reference: TensorFlow's ResourceApplyAdam takes its temporaries
+ * from the framework allocator.  This one is for callers that may not allocate device
+ * memory at all -- a framework op whose memory must all come from the framework's
+ * allocator (a TF / Horovod custom-op Compute()), a latency-critical loop, a process with
+ * a fixed memory budget.  It is the n == 1 fused Adam apply of b2dp_step on CALLER-OWNED
+ * arrays: w, m, v are updated in place from g (all fp32 device pointers on the current
+ * device, 16-byte aligned, numel elements; same one-rounding-per-operation arithmetic, so
+ * w, m, v come out bit-identical to b2dp_step), and stats_out (2 doubles, device memory)
+ * receives [sum of squares of the scaled gradient, count of non-finite gradient elements].
+ * The scratch the statistics reduction needs is a static __device__ array inside the
+ * library (128.25 KB on every GPU that loads it, held until exit) instead of an
+ * allocation, which fixes the largest call: numel > B2DP_NOALLOC_MAX_ELEMS returns
+ * B2DP_ERR_TOO_LARGE.  No cudaMalloc/cudaFree, no plan, no context.
+ *   - The first call on each device resolves the scratch array's device address
+ *     (cudaGetSymbolAddress) and the launch geometry; make that first call outside any
+ *     stream capture.
+ *   - Every call on a device shares the one scratch array.  Calls ordered on one stream
+ *     (or otherwise serialised) are fine; calls that overlap on the GPU race on it.
+ *   - hyper: lr, beta1, beta2, eps, step (>= 1), postscale are used; the rest ignored. */
+#define B2DP_NOALLOC_MAX_ELEMS 67108864LL /* 2^26 elements per call */
+int b2dp_adam_apply_noalloc(float* w, float* m, float* v, const float* g, int64_t numel,
+                            const b2dp_hyper* hyper, double* stats_out, void* stream);
+
 /* ----------------------------------------------------------- rank bootstrap helper --
  * Moves one fd per rank between the processes of a job over abstract unix datagram
  * sockets (SCM_RIGHTS).  `session` must be the same string on every rank and unique to

@@ -12,6 +12,7 @@ ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_ARCH, ERR_STATE, ERR_TIMEOUT, ERR_SYS,
 F32, BF16 = 0, 1
 OPT_NONE, OPT_ADAM, OPT_SGDM = 0, 1, 2
 BUF_GRADS, BUF_WEIGHTS, BUF_REDUCED, BUF_STATE0, BUF_STATE1, BUF_STATS = range(6)
+NOALLOC_MAX_ELEMS = 1 << 26
 
 
 class Hyper(ctypes.Structure):
@@ -68,6 +69,7 @@ SIGNATURES = {
     "b2dp_unpack": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(_vp), _vp]),
     "b2dp_load_weights": (ctypes.c_int, [_vp, _i32, ctypes.POINTER(_vp), _vp]),
     "b2dp_adam_alpha": (ctypes.c_float, [ctypes.c_float, ctypes.c_float, ctypes.c_float, _i64]),
+    "b2dp_adam_apply_noalloc": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i64, ctypes.POINTER(Hyper), _vp, _vp]),
     "b2dp_fd_exchange": (ctypes.c_int, [_i32, _i32, ctypes.c_char_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int), _i32]),
 }
 

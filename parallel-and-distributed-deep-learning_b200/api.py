@@ -32,6 +32,22 @@ def adam_alpha(lr, beta1, beta2, step):
     return float(_lib.load().b2dp_adam_alpha(lr, beta1, beta2, int(step)))
 
 
+def adam_apply_noalloc(w, m, v, g, hyper, stats_out, stream=None):
+    """b2dp_adam_apply_noalloc on caller-owned torch tensors (fp32, contiguous, on the current
+    device): the fused Adam apply for callers that may not allocate device memory.  The
+    library's only scratch is a fixed static device array, so at most 2**26 elements per
+    call, and calls that overlap on the GPU race on that array (see include/b200dp.h)."""
+    n = w.numel()
+    if not (m.numel() == n and v.numel() == n and g.numel() == n):
+        raise ValueError("adam_apply_noalloc: w, m, v, g must have the same number of elements")
+    if stats_out.numel() < 2:
+        raise ValueError("adam_apply_noalloc: stats_out needs 2 float64 elements")
+    vp = ctypes.c_void_p
+    check(_lib.load().b2dp_adam_apply_noalloc(vp(w.data_ptr()), vp(m.data_ptr()), vp(v.data_ptr()),
+                                              vp(g.data_ptr()), n, ctypes.byref(hyper), vp(stats_out.data_ptr()),
+                                              _stream_handle(stream, w.device.index)))
+
+
 class Layout:
     """The bucketing layer: K tensors -> buckets -> per-rank slices (host arithmetic only)."""
 

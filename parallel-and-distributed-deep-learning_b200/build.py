@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200dp.so")
-SOURCES = ["api.cu", "vmm.cpp", "layout.cpp", "fdxchg.cpp"]
+SOURCES = ["api.cu", "noalloc.cu", "vmm.cpp", "layout.cpp", "fdxchg.cpp"]
 HEADERS = ["kernels.cuh", "internal.h", os.path.join("..", "..", "include", "b200dp.h")]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
