@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=256, help="images per GPU (BASELINE.json configs[1])")
     ap.add_argument("--optimizer", default="adam", choices=["adam", "sgdm"])
     ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--path", default="auto", choices=["auto", "peer", "multicast"],
+                    help="N>1 collective path: peer loads with rank-order sum (bit-exact) or NVSwitch multicast")
     ap.add_argument("--hotpath-only", action="store_true", help="time only pack+step on synthetic gradients")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-batch", type=int, default=32, help="CPU arm: images per step (configs[0])")
@@ -204,6 +206,7 @@ def workload_config(args, n, cpu=False):
                     "224x224x3, batch %d/GPU, Adam; gradient SUM + optimizer apply via b200dp" % args.batch,
         "global_batch": (args.ref_batch if cpu else args.batch * n), "per_gpu_batch": args.ref_batch if cpu else args.batch,
         "optimizer": args.optimizer, "wire_dtype": args.wire, "parallelism": "dp%d" % n,
+        "collective_path": getattr(args, "path_used", "n/a"),
         "conv_graph": "torch-CPU stand-in" if cpu else "torch+cuDNN stand-in (TF32 convs, as TF defaults)",
         "l2": "inputs_exceed_l2 (activations and 409 MB of w/m/v/g per step >> 126 MB L2)",
     }
@@ -242,7 +245,18 @@ def run_b200dp(args):
         dist.broadcast_object_list(obj, src=0)
         plan.exchange(obj[0])
         dist.barrier()
+        # auto: the multicast path only pays from 5 ranks up (r01 sweep: n=2 peer 176 vs mc 274 us,
+        # n=4 251 vs 247, n=8 294 vs 241); below that the bit-exact peer path is also the faster one
+        want_mc = args.path == "multicast" or (args.path == "auto" and n > 4)
+        if want_mc and args.wire == "f32":
+            try:
+                plan.enable_multicast(obj[0])
+            except b200dp.B200dpError:
+                if args.path == "multicast":
+                    raise
+        dist.barrier()
 
+    args.path_used = plan.path if n > 1 else "n/a (single GPU)"
     B = args.batch
     gen = torch.Generator(device=device).manual_seed(7 + rank)
     host_gen = torch.Generator().manual_seed(7 + rank)
@@ -362,6 +376,33 @@ def run_b200dp(args):
     pack_med_ms, pack_avg_ms = time_region(only_pack, reps)
     plan.check(0)
 
+    ar_med_ms = None
+    if n > 1:
+        only_pack()
+        ar_med_ms, _ = time_region(lambda: plan.allreduce(0, postscale=1.0 / n), reps)
+        plan.check(0)
+
+    other = {}
+    if n > 1 and plan.path == "multicast":   # the deterministic peer path on the same buffers, for the record
+        plan.set_path("peer")
+        for _ in range(3):
+            pack_and_step()
+        other["peer_path_step_us"] = time_region(only_step, reps)[1] * 1e3
+        only_pack()
+        other["peer_path_allreduce_only_us"] = time_region(lambda: plan.allreduce(0, postscale=1.0 / n), reps)[0] * 1e3
+        plan.check(0)
+        plan.set_path("multicast")
+
+    # NCCL on the same box, same 102.33 MB fp32 message: the library call the reference's
+    # strategies bottom out in, timed the same way (the bar to beat)
+    nccl_med_ms = None
+    if n > 1:
+        buf = torch.randn(N_ELEMS, device=device) * 1e-3
+        for _ in range(5):
+            dist.all_reduce(buf)
+        nccl_med_ms, _ = time_region(lambda: dist.all_reduce(buf), reps)
+        del buf
+
     e2e = None
     if step_e2e is not None:
         ms_e2e = timed(step_e2e, args.steps, args.warmup)
@@ -388,9 +429,13 @@ def run_b200dp(args):
                     "traffic": load_traffic("step_n1")}
     else:
         wire_b = 2 if args.wire == "bf16" else 4
-        nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S   # per GPU per direction: RS reads in + AG writes in
+        if plan.path == "multicast":   # inbound: S/n reduced + (n-1)/n*S replicated stores; outbound the mirror image
+            nvl_bytes = float(S)
+        else:                          # per GPU per direction: RS reads in + AG writes in
+            nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S
         achieved = nvl_bytes / (step_avg_ms * 1e-3) / 1e9
-        roofline = {"kernel": "step_kernel<N=%d,%s,%s> (reduce-scatter + apply + all-gather over NVLink peer memory)"
+        roofline = {"kernel": ("step_mc_kernel<%s> (multimem.ld_reduce + apply + multimem.st through NVSwitch, N=%d)" % (args.optimizer, n)) if plan.path == "multicast" else
+                              "step_kernel<N=%d,%s,%s> (reduce-scatter + apply + all-gather over NVLink peer memory)"
                               % (n, args.wire, args.optimizer),
                     "bound": "nvlink", "achieved": achieved, "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
                     "frac": achieved / NVLINK_PEAK_GBS,
@@ -402,6 +447,13 @@ def run_b200dp(args):
                 "allreduce_busbw_gbs": busbw, "busbw_vs_900": busbw / 900.0,
                 "pack_hbm_gbs": (4 + (2 if args.wire == "bf16" else 4)) * N_ELEMS / (pack_avg_ms * 1e-3) / 1e9,
                 "elems_per_rank": elems_per_rank}
+    hot_path.update(other)
+    if ar_med_ms:
+        hot_path["allreduce_only_us"] = ar_med_ms * 1e3
+        hot_path["allreduce_only_busbw_gbs"] = (S / (ar_med_ms * 1e-3)) * 2 * (n - 1) / n / 1e9
+    if nccl_med_ms:
+        hot_path["nccl_allreduce_us"] = nccl_med_ms * 1e3
+        hot_path["nccl_busbw_gbs"] = (S / (nccl_med_ms * 1e-3)) * 2 * (n - 1) / n / 1e9
 
     line = {
         "metric": METRIC if not args.hotpath_only else "hot_path_steps_per_sec_as_images",

@@ -148,6 +148,34 @@ int b2dp_plan_buffer(b2dp_plan* p, int32_t dev, int32_t which, void** ptr, int64
  * B2DP_OK or B2DP_ERR_TIMEOUT. */
 int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream);
 
+/* Path B -- NVSwitch multicast (NVLS).  The default collective path (B2DP_PATH_PEER) pulls
+ * slices with peer loads and sums them in rank order: bit-identical to TF's AddN.  When the
+ * box has an NVSwitch with multicast, a plan can instead bind every rank's block to one
+ * multicast object; b2dp_step / b2dp_allreduce then use multimem.ld_reduce (the switch
+ * adds the n copies) and multimem.st (the switch replicates the store): about S bytes per
+ * GPU per direction instead of 2(n-1)/n*S, at the price of the switch's own summation
+ * order (parity within (n-1)*2^-24*sum|g_i|, not bitwise) -- the same trade NCCL's NVLS
+ * all-reduce makes under MultiWorkerMirroredStrategy(NCCL) (-multiworkers.py:20-21).
+ * f32 wire only.  Local context: multicast_create does everything (fd_out = -1).
+ * Rank contexts: rank 0 calls multicast_create and ships the fd to every rank; every rank
+ * calls multicast_join(fd); after ALL ranks joined, every rank calls multicast_bind; after
+ * ALL ranks bound, set_path(B2DP_PATH_MULTICAST). */
+typedef enum { B2DP_PATH_PEER = 0, B2DP_PATH_MULTICAST = 1 } b2dp_path;
+int b2dp_plan_multicast_create(b2dp_plan* p, int* fd_out);
+int b2dp_plan_multicast_join(b2dp_plan* p, int fd);
+int b2dp_plan_multicast_bind(b2dp_plan* p);
+int b2dp_plan_set_path(b2dp_plan* p, int32_t path);
+int32_t b2dp_plan_path(const b2dp_plan* p);
+/* Launch-geometry knobs of the collective kernels (every rank must set the same values:
+ * all ranks launch the same grid).  Defaults come from sweeps on 8xB200 (profiles/). */
+typedef enum {
+  B2DP_TUNE_GRID_CAP = 0,    /* peer path: max blocks (<= 1024, also bounded by co-residency) */
+  B2DP_TUNE_MC_GRID_CAP = 1, /* multicast path: max blocks */
+  B2DP_TUNE_MC_UNROLL = 2,   /* multicast path: vectors in flight per thread (1, 2, 4) */
+  B2DP_TUNE_PEER_UNROLL = 3  /* peer path: 0 = automatic, 1 or 2 */
+} b2dp_tune;
+int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value);
+
 /* --------------------------------------------------------------------- the hot path --
  * (1) pack: gather + cast + prescale the bucket's gradient tensors into the wire buffer.
  * One launch over a device-resident (pointer, offset, count) tile table.  Replaces

@@ -13,6 +13,8 @@ F32, BF16 = 0, 1
 OPT_NONE, OPT_ADAM, OPT_SGDM = 0, 1, 2
 BUF_GRADS, BUF_WEIGHTS, BUF_REDUCED, BUF_STATE0, BUF_STATE1, BUF_STATS = range(6)
 NOALLOC_MAX_ELEMS = 1 << 26
+PATH_PEER, PATH_MULTICAST = 0, 1
+TUNE = {"grid_cap": 0, "mc_grid_cap": 1, "mc_unroll": 2, "peer_unroll": 3}
 
 
 class Hyper(ctypes.Structure):
@@ -61,6 +63,12 @@ SIGNATURES = {
     "b2dp_plan_ready": (_i32, [_vp]),
     "b2dp_plan_buffer": (ctypes.c_int, [_vp, _i32, _i32, ctypes.POINTER(_vp), ctypes.POINTER(_i64)]),
     "b2dp_plan_check": (ctypes.c_int, [_vp, _i32, _vp]),
+    "b2dp_plan_multicast_create": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_int)]),
+    "b2dp_plan_multicast_join": (ctypes.c_int, [_vp, ctypes.c_int]),
+    "b2dp_plan_multicast_bind": (ctypes.c_int, [_vp]),
+    "b2dp_plan_set_path": (ctypes.c_int, [_vp, _i32]),
+    "b2dp_plan_path": (_i32, [_vp]),
+    "b2dp_plan_set_tuning": (ctypes.c_int, [_vp, _i32, _i32]),
     "b2dp_pack": (ctypes.c_int, [_vp, _i32, _i32, ctypes.POINTER(_vp), _i32, ctypes.c_float, _vp]),
     "b2dp_step": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(Hyper), _vp]),
     "b2dp_allreduce": (ctypes.c_int, [_vp, _i32, _i32, ctypes.c_float, _vp]),

@@ -196,6 +196,55 @@ class Plan:
                 if fds[r] >= 0:
                     os.close(fds[r])
 
+    def enable_multicast(self, session=None, timeout_ms=60000):
+        """Path B: binds every rank's block to one NVSwitch multicast object and switches the
+        collectives to multimem.ld_reduce / multimem.st.  Raises if the box has no multicast.
+        For rank contexts `session` must be a job-unique string (as for exchange())."""
+        L = self._L
+        if self.ctx.is_local:
+            check(L.b2dp_plan_multicast_create(self._h, None))
+        else:
+            n, rank = self.ctx.nranks, self.ctx.ranks[0]
+            own = ctypes.c_int(-1)
+            check(L.b2dp_plan_export_fd(self._h, ctypes.byref(own)))   # dummy payload for ranks != 0
+            mcfd = ctypes.c_int(-1)
+            try:
+                if rank == 0:
+                    check(L.b2dp_plan_multicast_create(self._h, ctypes.byref(mcfd)))
+                fds = (ctypes.c_int * n)()
+
+                def rendezvous(tag, payload):
+                    check(L.b2dp_fd_exchange(rank, n, ("%s-%s" % (session, tag)).encode(), payload, fds, int(timeout_ms)))
+                    got = [fds[r] for r in range(n)]
+                    return got
+
+                got = rendezvous("mc0", mcfd.value if rank == 0 else own.value)
+                check(L.b2dp_plan_multicast_join(self._h, got[0]))
+                for f in got:
+                    os.close(f)
+                for f in rendezvous("mc1", own.value):     # everyone has joined
+                    os.close(f)
+                check(L.b2dp_plan_multicast_bind(self._h))
+                for f in rendezvous("mc2", own.value):     # everyone has bound
+                    os.close(f)
+            finally:
+                os.close(own.value)
+                if mcfd.value >= 0:
+                    os.close(mcfd.value)
+        check(L.b2dp_plan_set_path(self._h, _lib.PATH_MULTICAST))
+
+    def set_path(self, path):
+        check(self._L.b2dp_plan_set_path(self._h, {"peer": _lib.PATH_PEER, "multicast": _lib.PATH_MULTICAST}.get(path, path)))
+
+    def set_tuning(self, **knobs):
+        """grid_cap / mc_grid_cap / mc_unroll / peer_unroll -- same values on every rank."""
+        for k, v in knobs.items():
+            check(self._L.b2dp_plan_set_tuning(self._h, _lib.TUNE[k], int(v)))
+
+    @property
+    def path(self):
+        return "multicast" if self._L.b2dp_plan_path(self._h) == _lib.PATH_MULTICAST else "peer"
+
     @property
     def ready(self):
         return bool(self._L.b2dp_plan_ready(self._h))

@@ -1,5 +1,6 @@
 // api.cu -- contexts, plans and kernel launchers behind include/b200dp.h.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 
@@ -87,6 +88,9 @@ struct RankState {
   PtrTable grads, outs, weights;
   uint32_t epoch = 0;
   int num_sms = 0;
+  // Path B: the plan's multicast object as seen by this rank
+  unsigned long long mc_handle = 0, mc_va = 0;
+  bool mc_owner = false, mc_joined = false, mc_bound = false;
 };
 
 }  // namespace
@@ -106,6 +110,13 @@ struct b2dp_plan {
   b2dp_layout layout;
   BlockMap map;
   std::vector<std::unique_ptr<RankState>> rs;
+  size_t block_bytes = 0;  // allocated size of every rank's block (granularity-rounded)
+  int path = B2DP_PATH_PEER;
+  // launch geometry knobs (b2dp_plan_set_tuning); defaults from the r01 sweeps on 8xB200
+  int grid_cap = kMaxBlocks;  // peer-path blocks (also bounded by co-residency)
+  int mc_grid_cap = 74;       // multicast path: fewer blocks contend less in the switch
+  int mc_unroll = 1;
+  int peer_unroll = 0;        // 0 = automatic (1 for n == 8, else 2)
 };
 
 namespace {
@@ -190,46 +201,56 @@ int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const v
 }
 
 template <typename KernelT>
-int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U) {
+int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_cap = kMaxBlocks) {
   int occ = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kStepThreads, 0) != cudaSuccess || occ < 1) {
     (void)cudaGetLastError();
     occ = 1;
   }
   int64_t want = (nvec + (int64_t)kStepThreads * U - 1) / ((int64_t)kStepThreads * U);
-  int64_t cap = std::min<int64_t>(kMaxBlocks, (int64_t)r.num_sms * occ);
+  int64_t cap = std::min<int64_t>(std::max(1, std::min(kMaxBlocks, grid_cap)), (int64_t)r.num_sms * occ);
   return (int)std::max<int64_t>(1, std::min(want, cap));
 }
 
-template <int N, typename WireT, int OPT>
-int launch_step_n(const RankState& r, const StepArgs& a, cudaStream_t s) {
-  constexpr int U = (N >= 8) ? 1 : 2;
+struct Tuning {
+  int grid_cap, unroll;
+};
+
+template <int N, typename WireT, int OPT, int U>
+int launch_step_u(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
   auto kernel = step_kernel<N, WireT, OPT, U>;
-  const int grid = step_grid(kernel, r, a.nvec, U);
+  const int grid = step_grid(kernel, r, a.nvec, U, t.grid_cap);
   kernel<<<grid, kStepThreads, 0, s>>>(a);
   CUDA_TRY(cudaGetLastError());
   return B2DP_OK;
 }
 
+template <int N, typename WireT, int OPT>
+int launch_step_n(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  const int u = t.unroll ? t.unroll : ((N >= 8) ? 1 : 2);
+  if (u == 1) return launch_step_u<N, WireT, OPT, 1>(r, a, t, s);
+  return launch_step_u<N, WireT, OPT, 2>(r, a, t, s);
+}
+
 template <typename WireT, int OPT>
-int launch_step_w(int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
+int launch_step_w(int n, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
   switch (n) {
-    case 1: return launch_step_n<1, WireT, OPT>(r, a, s);
-    case 2: return launch_step_n<2, WireT, OPT>(r, a, s);
-    case 3: return launch_step_n<3, WireT, OPT>(r, a, s);
-    case 4: return launch_step_n<4, WireT, OPT>(r, a, s);
-    case 5: return launch_step_n<5, WireT, OPT>(r, a, s);
-    case 6: return launch_step_n<6, WireT, OPT>(r, a, s);
-    case 7: return launch_step_n<7, WireT, OPT>(r, a, s);
-    case 8: return launch_step_n<8, WireT, OPT>(r, a, s);
+    case 1: return launch_step_n<1, WireT, OPT>(r, a, t, s);
+    case 2: return launch_step_n<2, WireT, OPT>(r, a, t, s);
+    case 3: return launch_step_n<3, WireT, OPT>(r, a, t, s);
+    case 4: return launch_step_n<4, WireT, OPT>(r, a, t, s);
+    case 5: return launch_step_n<5, WireT, OPT>(r, a, t, s);
+    case 6: return launch_step_n<6, WireT, OPT>(r, a, t, s);
+    case 7: return launch_step_n<7, WireT, OPT>(r, a, t, s);
+    case 8: return launch_step_n<8, WireT, OPT>(r, a, t, s);
   }
   return fail(B2DP_ERR_INVALID, "unsupported rank count %d", n);
 }
 
 template <int OPT>
-int launch_step_o(int wire, int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
-  if (wire == B2DP_F32) return launch_step_w<float, OPT>(n, r, a, s);
-  return launch_step_w<__nv_bfloat16, OPT>(n, r, a, s);
+int launch_step_o(int wire, int n, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  if (wire == B2DP_F32) return launch_step_w<float, OPT>(n, r, a, t, s);
+  return launch_step_w<__nv_bfloat16, OPT>(n, r, a, t, s);
 }
 
 int launch_gather(int n, const RankState& r, const StepArgs& a, cudaStream_t s) {
@@ -252,6 +273,28 @@ int launch_gather(int n, const RankState& r, const StepArgs& a, cudaStream_t s) 
   }
   if (e != cudaSuccess) return fail(B2DP_ERR_CUDA, "gather launch: %s", cudaGetErrorString(e));
   return B2DP_OK;
+}
+
+template <int OPT, int U>
+int launch_step_mc_u(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  auto kernel = step_mc_kernel<OPT, U>;
+  const int grid = step_grid(kernel, r, a.nvec, U, t.grid_cap);
+  kernel<<<grid, kStepThreads, 0, s>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return B2DP_OK;
+}
+
+template <int OPT>
+int launch_step_mc_o(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  if (t.unroll == 1) return launch_step_mc_u<OPT, 1>(r, a, t, s);
+  if (t.unroll == 2) return launch_step_mc_u<OPT, 2>(r, a, t, s);
+  return launch_step_mc_u<OPT, 4>(r, a, t, s);
+}
+
+int launch_step_mc(int opt, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  if (opt == B2DP_OPT_ADAM) return launch_step_mc_o<B2DP_OPT_ADAM>(r, a, t, s);
+  if (opt == B2DP_OPT_SGDM) return launch_step_mc_o<B2DP_OPT_SGDM>(r, a, t, s);
+  return launch_step_mc_o<B2DP_OPT_NONE>(r, a, t, s);
 }
 
 int fill_comm(b2dp_plan* p, RankState& r, Comm* c) {
@@ -328,26 +371,36 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     a.push = (mode == 1) ? 0 : 1;
     fill_comm(p, r, &a.c);
     int rc;
-    if (mode == 3)
+    const bool use_mc = p->path == B2DP_PATH_MULTICAST && a.c.use_flags && (mode == 0 || mode == 2);
+    if (use_mc) {
+      char* mc = reinterpret_cast<char*>(r.mc_va);
+      a.g[0] = mc + p->map.grads + slice_elem0 * wire;
+      a.out[0] = reinterpret_cast<float*>(mc + out_off + slice_elem0 * 4);
+      a.w = reinterpret_cast<float*>(r.base[r.rank] + out_off + slice_elem0 * 4);
+      rc = launch_step_mc(opt, r, a, Tuning{p->mc_grid_cap, p->mc_unroll}, s);
+    } else if (mode == 3)
       rc = launch_gather(n, r, a, s);
     else if (opt == B2DP_OPT_ADAM)
-      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, s);
+      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
     else if (opt == B2DP_OPT_SGDM)
-      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, s);
+      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
     else
-      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, s);
+      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
     if (rc) return rc;
   }
   return B2DP_OK;
 }
 
-void destroy_rank(RankState& r) {
+void destroy_rank(RankState& r, size_t block_bytes = 0, bool local = true) {
   if (r.device < 0) return;
   DeviceGuard guard(r.device);
   cudaDeviceSynchronize();
   if (r.d_tiles) cudaFree(r.d_tiles);
   for (PtrTable* t : {&r.grads, &r.outs, &r.weights})
     if (t->dev) cudaFree(t->dev);
+  // local context: every rank shares one multicast handle/mapping and the owner frees it;
+  // rank context: this process holds its own (created or imported) handle and mapping
+  if (r.mc_handle && (r.mc_owner || !local)) mc_release(r.mc_handle, r.mc_va, block_bytes);
   for (auto& b : r.imported) vmm_free(&b);
   vmm_free(&r.own);
   (void)cudaGetLastError();
@@ -419,7 +472,12 @@ extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** o
     DeviceGuard guard(r->device);
     CUDA_TRY(cudaFree(0));  // make sure the primary context exists before driver calls
     CUDA_TRY(cudaDeviceGetAttribute(&r->num_sms, cudaDevAttrMultiProcessorCount, r->device));
-    int rc = vmm_alloc(r->device, p->map.end, c->devices, c->nlocal, &r->own);
+    size_t gran = 0, mgran = 0;
+    if (int rc0 = vmm_granularity(r->device, &gran)) return rc0;
+    if (c->nranks > 1 && !c->emulated && mc_granularity(c->nranks, 1 << 21, &mgran) == B2DP_OK && mgran > gran)
+      gran = mgran;  // keep the block bindable to a multicast object
+    p->block_bytes = align_up(p->map.end, gran);
+    int rc = vmm_alloc(r->device, p->block_bytes, c->devices, c->nlocal, &r->own);
     if (rc) {
       for (auto& q : p->rs) destroy_rank(*q);
       return rc;
@@ -446,7 +504,7 @@ extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** o
 
 extern "C" void b2dp_plan_destroy(b2dp_plan* p) {
   if (!p) return;
-  for (auto& r : p->rs) destroy_rank(*r);
+  for (auto& r : p->rs) destroy_rank(*r, p->block_bytes, p->ctx->local);
   delete p;
 }
 
@@ -511,6 +569,112 @@ extern "C" int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream) {
     return fail(st, "rank %d: a cross-GPU flag wait timed out (a peer never reached the collective)", r->rank);
   }
   return B2DP_OK;
+}
+
+// ------------------------------------------------------------- Path B: NVSwitch multicast
+extern "C" int b2dp_plan_multicast_create(b2dp_plan* p, int* fd_out) {
+  if (!p) return fail(B2DP_ERR_INVALID, "multicast_create: plan is null");
+  if (fd_out) *fd_out = -1;
+  const int n = p->ctx->nranks;
+  if (n < 2 || p->ctx->emulated) return fail(B2DP_ERR_STATE, "multicast_create: needs >= 2 distinct GPUs");
+  if (p->layout.wire != B2DP_F32) return fail(B2DP_ERR_STATE, "multicast_create: Path B carries an f32 wire only");
+  if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "multicast_create: attach the peers first");
+  RankState& r0 = *p->rs[0];
+  if (r0.mc_handle) return fail(B2DP_ERR_STATE, "multicast_create: already created");
+  for (auto& r : p->rs)
+    if (int rc = mc_supported(r->device)) return rc;
+  if (!p->ctx->local && r0.rank != 0) return fail(B2DP_ERR_STATE, "multicast_create: only rank 0 creates the object");
+  DeviceGuard guard(r0.device);
+  unsigned long long h = 0;
+  if (int rc = mc_create(n, p->block_bytes, &h)) return rc;
+  if (p->ctx->local) {
+    // one process: add every device, bind every block, map once for all devices
+    for (auto& r : p->rs)
+      if (int rc = mc_add_device(h, r->device)) return rc;
+    for (auto& r : p->rs) {
+      DeviceGuard g2(r->device);
+      if (int rc = mc_bind(h, r->own, p->block_bytes)) return rc;
+    }
+    unsigned long long va = 0;
+    if (int rc = mc_map(h, p->block_bytes, p->ctx->devices, p->ctx->nlocal, &va)) return rc;
+    for (auto& r : p->rs) {
+      r->mc_handle = h;
+      r->mc_va = va;
+      r->mc_joined = r->mc_bound = true;
+    }
+    r0.mc_owner = true;
+    return B2DP_OK;
+  }
+  r0.mc_handle = h;
+  r0.mc_owner = true;
+  if (!fd_out) return fail(B2DP_ERR_INVALID, "multicast_create: fd_out is required for a rank context");
+  return mc_export_fd(h, fd_out);
+}
+
+extern "C" int b2dp_plan_multicast_join(b2dp_plan* p, int fd) {
+  if (!p) return fail(B2DP_ERR_INVALID, "multicast_join: plan is null");
+  if (p->ctx->local) return fail(B2DP_ERR_STATE, "multicast_join: a local context joins inside multicast_create");
+  RankState& r = *p->rs[0];
+  if (r.mc_joined) return fail(B2DP_ERR_STATE, "multicast_join: already joined");
+  DeviceGuard guard(r.device);
+  if (!r.mc_owner) {
+    if (int rc = mc_supported(r.device)) return rc;
+    if (int rc = mc_import_fd(fd, &r.mc_handle)) return rc;
+  }
+  if (int rc = mc_add_device(r.mc_handle, r.device)) return rc;
+  r.mc_joined = true;
+  return B2DP_OK;
+}
+
+extern "C" int b2dp_plan_multicast_bind(b2dp_plan* p) {
+  if (!p) return fail(B2DP_ERR_INVALID, "multicast_bind: plan is null");
+  if (p->ctx->local) return fail(B2DP_ERR_STATE, "multicast_bind: a local context binds inside multicast_create");
+  RankState& r = *p->rs[0];
+  if (!r.mc_joined) return fail(B2DP_ERR_STATE, "multicast_bind: join first (and wait until every rank has joined)");
+  if (r.mc_bound) return B2DP_OK;
+  DeviceGuard guard(r.device);
+  if (int rc = mc_bind(r.mc_handle, r.own, p->block_bytes)) return rc;
+  if (int rc = mc_map(r.mc_handle, p->block_bytes, &r.device, 1, &r.mc_va)) return rc;
+  r.mc_bound = true;
+  return B2DP_OK;
+}
+
+extern "C" int b2dp_plan_set_path(b2dp_plan* p, int32_t path) {
+  if (!p) return fail(B2DP_ERR_INVALID, "set_path: plan is null");
+  if (path == B2DP_PATH_PEER) {
+    p->path = path;
+    return B2DP_OK;
+  }
+  if (path != B2DP_PATH_MULTICAST) return fail(B2DP_ERR_INVALID, "set_path: unknown path %d", path);
+  for (auto& r : p->rs)
+    if (!r->mc_bound) return fail(B2DP_ERR_STATE, "set_path: the plan's multicast object is not bound (multicast_create/join/bind)");
+  p->path = path;
+  return B2DP_OK;
+}
+
+extern "C" int32_t b2dp_plan_path(const b2dp_plan* p) { return p ? p->path : -1; }
+
+extern "C" int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value) {
+  if (!p) return fail(B2DP_ERR_INVALID, "set_tuning: plan is null");
+  switch (key) {
+    case B2DP_TUNE_GRID_CAP:
+      if (value < 1) return fail(B2DP_ERR_INVALID, "set_tuning: grid cap must be >= 1");
+      p->grid_cap = value;
+      return B2DP_OK;
+    case B2DP_TUNE_MC_GRID_CAP:
+      if (value < 1) return fail(B2DP_ERR_INVALID, "set_tuning: grid cap must be >= 1");
+      p->mc_grid_cap = value;
+      return B2DP_OK;
+    case B2DP_TUNE_MC_UNROLL:
+      if (value != 1 && value != 2 && value != 4) return fail(B2DP_ERR_INVALID, "set_tuning: multicast unroll is 1, 2 or 4");
+      p->mc_unroll = value;
+      return B2DP_OK;
+    case B2DP_TUNE_PEER_UNROLL:
+      if (value < 0 || value > 2) return fail(B2DP_ERR_INVALID, "set_tuning: peer unroll is 0 (auto), 1 or 2");
+      p->peer_unroll = value;
+      return B2DP_OK;
+  }
+  return fail(B2DP_ERR_INVALID, "set_tuning: unknown key %d", key);
 }
 
 // ------------------------------------------------------------------------- the hot path

@@ -70,4 +70,15 @@ int vmm_export_fd(const VmmBlock& b, int* fd);
 int vmm_import_fd(int fd, size_t size, int device, VmmBlock* out);
 void vmm_free(VmmBlock* b);
 
+// NVSwitch multicast objects (Path B); every function returns B2DP_OK or an error
+int mc_supported(int device);
+int mc_granularity(int ndev, size_t size, size_t* gran);
+int mc_create(int ndev, size_t size, unsigned long long* handle);
+int mc_export_fd(unsigned long long handle, int* fd);
+int mc_import_fd(int fd, unsigned long long* handle);
+int mc_add_device(unsigned long long handle, int device);
+int mc_bind(unsigned long long handle, const VmmBlock& mem, size_t size);
+int mc_map(unsigned long long handle, size_t size, const int* devs, int ndev, unsigned long long* va_out);
+void mc_release(unsigned long long handle, unsigned long long va, size_t size);
+
 }  // namespace b2dp

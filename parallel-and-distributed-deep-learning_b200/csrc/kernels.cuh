@@ -47,6 +47,21 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// NVSwitch multicast (NVLS): one load that the switch answers with the sum over every
+// GPU's copy, one store that the switch replicates into every GPU's copy.
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f4(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float4* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -348,6 +363,74 @@ step_kernel(const StepArgs a) {
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
 
   flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
+}
+
+// Path B: the same step through the NVSwitch multicast mapping.  a.g[0] / a.out[0] are
+// MULTICAST addresses of this rank's slice: the reduce-scatter is one multimem.ld_reduce
+// per vector (the switch adds the n copies -- in its own order, so this path is checked
+// against the oracle under the order-free tolerance, not bitwise) and the all-gather one
+// multimem.st.  Per GPU and direction only ~S bytes cross NVLink instead of 2(n-1)/n*S.
+template <int OPT, int U>
+__global__ void __launch_bounds__(kStepThreads)
+step_mc_kernel(const StepArgs a) {
+  flag_barrier(a.c, 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float sumsq = 0.0f;
+  float bad = 0.0f;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < a.nvec; base += stride * U) {
+    float4 g[U], w[U], s0[U], s1[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < a.nvec) {
+        g[u] = multimem_ld_reduce_add_f4(reinterpret_cast<const float4*>(a.g[0]) + q);
+        if (OPT != B2DP_OPT_NONE) {
+          w[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q);
+          s0[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.s0) + q);
+          if (OPT == B2DP_OPT_ADAM) s1[u] = ld_stream_f4(reinterpret_cast<const float4*>(a.s1) + q);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < a.nvec) {
+        float4 acc = g[u];
+        acc.x = __fmul_rn(acc.x, a.o.postscale);
+        acc.y = __fmul_rn(acc.y, a.o.postscale);
+        acc.z = __fmul_rn(acc.z, a.o.postscale);
+        acc.w = __fmul_rn(acc.w, a.o.postscale);
+        if (a.want_stats) {
+          sumsq = fmaf(acc.x, acc.x, fmaf(acc.y, acc.y, fmaf(acc.z, acc.z, fmaf(acc.w, acc.w, sumsq))));
+          bad += (float)(!isfinite(acc.x)) + (float)(!isfinite(acc.y)) + (float)(!isfinite(acc.z)) +
+                 (float)(!isfinite(acc.w));
+        }
+        float4 res;
+        if (OPT == B2DP_OPT_ADAM) {
+          adam_update(acc.x, w[u].x, s0[u].x, s1[u].x, a.o);
+          adam_update(acc.y, w[u].y, s0[u].y, s1[u].y, a.o);
+          adam_update(acc.z, w[u].z, s0[u].z, s1[u].z, a.o);
+          adam_update(acc.w, w[u].w, s0[u].w, s1[u].w, a.o);
+          st_f4(reinterpret_cast<float4*>(a.s0) + q, s0[u]);
+          st_f4(reinterpret_cast<float4*>(a.s1) + q, s1[u]);
+          res = w[u];
+        } else if (OPT == B2DP_OPT_SGDM) {
+          sgdm_update(acc.x, w[u].x, s0[u].x, a.o);
+          sgdm_update(acc.y, w[u].y, s0[u].y, a.o);
+          sgdm_update(acc.z, w[u].z, s0[u].z, a.o);
+          sgdm_update(acc.w, w[u].w, s0[u].w, a.o);
+          if (a.o.mu != 0.0f) st_f4(reinterpret_cast<float4*>(a.s0) + q, s0[u]);
+          res = w[u];
+        } else {
+          res = acc;
+        }
+        multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + q, res);
+      }
+    }
+  }
+  if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
+  __threadfence_system();  // multicast stores are performed everywhere before the exit flags go out
+  flag_barrier(a.c, 1);
 }
 
 // all-gather alone: push this rank's weight slice into every rank's weight buffer

@@ -39,6 +39,15 @@ struct Driver {
                                          unsigned long long) = nullptr;
   CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle*, void*,
                                            CUmemAllocationHandleType) = nullptr;
+  // NVSwitch multicast (optional: absent on drivers/boxes without NVLS)
+  bool mc_ok = false;
+  CUresult (*MulticastCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*) = nullptr;
+  CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
+  CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t,
+                               unsigned long long) = nullptr;
+  CUresult (*MulticastGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags) = nullptr;
+  CUresult (*DeviceGet)(CUdevice*, int) = nullptr;
+  CUresult (*DeviceGetAttribute)(int*, CUdevice_attribute, CUdevice) = nullptr;
 };
 
 Driver g_drv;
@@ -72,6 +81,13 @@ void init_once() {
             resolve("cuMemImportFromShareableHandle", &d.MemImportFromShareableHandle, &why);
   d.ok = ok;
   d.why = why;
+  std::string why_mc;
+  d.mc_ok = ok && resolve("cuMulticastCreate", &d.MulticastCreate, &why_mc) &&
+            resolve("cuMulticastAddDevice", &d.MulticastAddDevice, &why_mc) &&
+            resolve("cuMulticastBindMem", &d.MulticastBindMem, &why_mc) &&
+            resolve("cuMulticastGetGranularity", &d.MulticastGetGranularity, &why_mc) &&
+            resolve("cuDeviceGet", &d.DeviceGet, &why_mc) &&
+            resolve("cuDeviceGetAttribute", &d.DeviceGetAttribute, &why_mc);
 }
 
 const char* cu_str(CUresult r) {
@@ -195,6 +211,94 @@ int vmm_import_fd(int fd, size_t size, int device, VmmBlock* out) {
   out->owner_device = -1;
   out->mapped = true;
   return B2DP_OK;
+}
+
+// ---- NVSwitch multicast objects (Path B) ------------------------------------------------
+namespace {
+CUmulticastObjectProp mc_prop(int ndev, size_t size) {
+  CUmulticastObjectProp prop;
+  memset(&prop, 0, sizeof prop);
+  prop.numDevices = (unsigned)ndev;
+  prop.size = size;
+  prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  return prop;
+}
+}  // namespace
+
+int mc_supported(int device) {
+  if (int rc = vmm_init()) return rc;
+  if (!g_drv.mc_ok) return fail(B2DP_ERR_CUDA, "this driver has no cuMulticast* entry points");
+  CUdevice d;
+  CU_TRY(g_drv.DeviceGet(&d, device), "cuDeviceGet");
+  int v = 0;
+  CU_TRY(g_drv.DeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d), "cuDeviceGetAttribute");
+  if (!v) return fail(B2DP_ERR_CUDA, "device %d does not support NVSwitch multicast", device);
+  return B2DP_OK;
+}
+
+int mc_granularity(int ndev, size_t size, size_t* gran) {
+  if (int rc = vmm_init()) return rc;
+  if (!g_drv.mc_ok) return fail(B2DP_ERR_CUDA, "this driver has no cuMulticast* entry points");
+  CUmulticastObjectProp prop = mc_prop(ndev, size);
+  CU_TRY(g_drv.MulticastGetGranularity(gran, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED), "cuMulticastGetGranularity");
+  return B2DP_OK;
+}
+
+int mc_create(int ndev, size_t size, unsigned long long* handle) {
+  if (int rc = vmm_init()) return rc;
+  if (!g_drv.mc_ok) return fail(B2DP_ERR_CUDA, "this driver has no cuMulticast* entry points");
+  CUmulticastObjectProp prop = mc_prop(ndev, size);
+  CUmemGenericAllocationHandle h = 0;
+  CU_TRY(g_drv.MulticastCreate(&h, &prop), "cuMulticastCreate");
+  *handle = h;
+  return B2DP_OK;
+}
+
+int mc_export_fd(unsigned long long handle, int* fd) {
+  int f = -1;
+  CU_TRY(g_drv.MemExportToShareableHandle(&f, handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0),
+         "cuMemExportToShareableHandle(multicast)");
+  *fd = f;
+  return B2DP_OK;
+}
+
+int mc_import_fd(int fd, unsigned long long* handle) {
+  if (int rc = vmm_init()) return rc;
+  CUmemGenericAllocationHandle h = 0;
+  CU_TRY(g_drv.MemImportFromShareableHandle(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR),
+         "cuMemImportFromShareableHandle(multicast)");
+  *handle = h;
+  return B2DP_OK;
+}
+
+int mc_add_device(unsigned long long handle, int device) {
+  CUdevice d;
+  CU_TRY(g_drv.DeviceGet(&d, device), "cuDeviceGet");
+  CU_TRY(g_drv.MulticastAddDevice(handle, d), "cuMulticastAddDevice");
+  return B2DP_OK;
+}
+
+int mc_bind(unsigned long long handle, const VmmBlock& mem, size_t size) {
+  CU_TRY(g_drv.MulticastBindMem(handle, 0, mem.handle, 0, size, 0), "cuMulticastBindMem");
+  return B2DP_OK;
+}
+
+int mc_map(unsigned long long handle, size_t size, const int* devs, int ndev, unsigned long long* va_out) {
+  size_t gran = 0;
+  if (int rc = vmm_granularity(devs[0], &gran)) return rc;
+  CUdeviceptr va = 0;
+  if (int rc = map_and_grant(handle, size, gran, devs, ndev, &va)) return rc;
+  *va_out = va;
+  return B2DP_OK;
+}
+
+void mc_release(unsigned long long handle, unsigned long long va, size_t size) {
+  if (!g_drv.ok) return;
+  if (va) {
+    g_drv.MemUnmap(va, size);
+    g_drv.MemAddressFree(va, size);
+  }
+  if (handle) g_drv.MemRelease(handle);
 }
 
 void vmm_free(VmmBlock* b) {

@@ -1,0 +1,315 @@
+"""Real multi-GPU parity (skipped on a one-GPU box; run with `gpurun --gpus 2|4|8`).
+
+ - local context over distinct GPUs (MirroredStrategy's shape: one process, peer access,
+   in-kernel flag barriers) vs the oracle, bit-exact;
+ - rank contexts, one process per GPU (Horovod / MWMS shape: fd exchange over unix sockets,
+   VMM import) vs the oracle bit-exact, and vs NCCL's all_reduce -- "the reference's
+   reduction as actually executed"  -- under the order-free tolerance
+   |err| <= (n-1) * 2^-24 * sum_i |g_i|."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+import b200dp  # noqa: E402
+import oracle  # noqa: E402
+
+F = np.float32
+NGPU = torch.cuda.device_count() if torch.cuda.is_available() else 0
+needs2 = pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=F).view(np.uint32)
+
+
+def host_grads(n, numels, step):
+    """Every rank can rebuild every rank's gradients (seeded per rank, tensor, step)."""
+    out = []
+    for r in range(n):
+        g = torch.Generator().manual_seed(1234 + 1000 * r + 100000 * step)
+        x = torch.randn(sum(numels), generator=g) * 1e-3
+        x[::5] += (-1.0) ** r * 50.0
+        out.append(x.numpy())
+    return out
+
+
+def views(flat, numels):
+    out, o = [], 0
+    for k in numels:
+        out.append(flat[o:o + k])
+        o += k
+    return out
+
+
+@needs2
+@pytest.mark.parametrize("wire", ["f32", "bf16"])
+def test_local_context_distinct_gpus_bit_exact(wire):
+    n = min(NGPU, 8)
+    numels = b200dp.resnet50_numels()
+    N = sum(numels)
+    ctx = b200dp.Context.local(list(range(n)))
+    ctx.set_timeout(5.0)
+    lay = b200dp.Layout(numels, nranks=n, wire=wire)
+    plan = b200dp.Plan(ctx, lay)
+    w0 = (torch.rand(N, generator=torch.Generator().manual_seed(42)) - 0.5) * 0.1
+    for r in range(n):
+        with torch.cuda.device(r):
+            plan.load_weights(r, views(w0.cuda(r), numels))
+    w_ref, m_ref, v_ref = w0.numpy().copy(), np.zeros(N, F), np.zeros(N, F)
+    for s in range(2):
+        hg = host_grads(n, numels, s)
+        dg = [torch.from_numpy(hg[r]).cuda(r) for r in range(n)]
+        for r in range(n):
+            with torch.cuda.device(r):
+                plan.pack(r, views(dg[r], numels))
+        for r in range(n):          # all ranks' kernels are in flight together; each waits for its peers
+            with torch.cuda.device(r):
+                plan.step(r, "adam", b200dp.adam_hyper(step=s + 1))
+        for r in range(n):
+            torch.cuda.synchronize(r)
+        oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(hg, bf16_wire=(wire == "bf16")), step=s + 1)
+    for r in range(n):
+        with torch.cuda.device(r):
+            plan.check(r)
+            got = plan.tensor(r, b200dp.BUF_WEIGHTS).cpu().numpy()
+        o = 0
+        for k, m in enumerate(numels):
+            off = lay.tensor_offset(k)
+            assert np.array_equal(bits(got[off:off + m]), bits(w_ref[o:o + m])), "rank %d tensor %d" % (r, k)
+            o += m
+
+
+def _rank_worker(rank, n, port, wire, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=n, device_id=torch.device("cuda", rank))
+    try:
+        numels = b200dp.resnet50_numels()
+        N = sum(numels)
+        ctx = b200dp.Context.rank(rank, n, rank)
+        ctx.set_timeout(5.0)
+        lay = b200dp.Layout(numels, nranks=n, wire=wire)
+        plan = b200dp.Plan(ctx, lay)
+        plan.exchange("t-%d" % port)
+        assert plan.ready
+        dist.barrier()
+        w0 = (torch.rand(N, generator=torch.Generator().manual_seed(42)) - 0.5) * 0.1
+        plan.load_weights(0, views(w0.cuda(), numels))
+        w_ref, m_ref, v_ref = w0.numpy().copy(), np.zeros(N, F), np.zeros(N, F)
+        ok_w = ok_ar = ok_nccl = True
+        for s in range(2):
+            hg = host_grads(n, numels, s)
+            mine = torch.from_numpy(hg[rank]).cuda()
+            gsum = oracle.addn(hg, bf16_wire=(wire == "bf16"))
+            # hvd-shaped op: all-reduce only
+            plan.pack(0, views(mine, numels))
+            plan.allreduce(0)
+            torch.cuda.synchronize()
+            red = plan.tensor(0, b200dp.BUF_REDUCED).cpu().numpy()
+            flat_red = np.concatenate([red[lay.tensor_offset(k):lay.tensor_offset(k) + m] for k, m in enumerate(numels)])
+            ok_ar &= bool(np.array_equal(bits(flat_red), bits(gsum)))
+            if wire == "f32":   # NCCL on the same inputs: order-free tolerance
+                t = mine.clone()
+                dist.all_reduce(t)
+                bound = (n - 1) * 2.0 ** -24 * np.sum(np.abs(np.stack(hg)), axis=0) + 1e-30
+                ok_nccl &= bool(np.all(np.abs(t.cpu().numpy().astype(np.float64) - gsum) <= bound))
+            # fused step (the all-reduce above ran in place, so pack again)
+            plan.pack(0, views(mine, numels))
+            plan.step(0, "adam", b200dp.adam_hyper(step=s + 1))
+            oracle.adam_(w_ref, m_ref, v_ref, gsum, step=s + 1)
+        torch.cuda.synchronize()
+        plan.check(0)
+        got = plan.tensor(0, b200dp.BUF_WEIGHTS).cpu().numpy()
+        flat_w = np.concatenate([got[lay.tensor_offset(k):lay.tensor_offset(k) + m] for k, m in enumerate(numels)])
+        ok_w = bool(np.array_equal(bits(flat_w), bits(w_ref)))
+        dist.barrier()
+        q.put((rank, ok_w, ok_ar, ok_nccl, ""))
+    except Exception as e:  # report instead of hanging the parent
+        import traceback
+        q.put((rank, False, False, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+@pytest.mark.parametrize("wire", ["f32", "bf16"])
+def test_rank_contexts_one_process_per_gpu(wire):
+    import torch.multiprocessing as mp
+    n = min(NGPU, 8)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank_worker, args=(r, n, port, wire, q)) for r in range(n)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(n)]
+    for p in procs:
+        p.join(60)
+    for rank, ok_w, ok_ar, ok_nccl, err in sorted(results):
+        assert not err, err
+        assert ok_ar, "rank %d: all-reduce differs from the oracle" % rank
+        assert ok_w, "rank %d: weights after 2 fused steps differ from the oracle" % rank
+        assert ok_nccl, "rank %d: NCCL all_reduce outside the order-free bound" % rank
+
+
+# ------------------------------------------------------------------ Path B (multicast)
+# The switch adds the n copies in its own order, so Path B is held to the order-free bound
+#   |sum_hat - sum| <= (n-1) * 2^-24 * sum_i |g_i|            ("Path B / NCCL-ordered")
+# for the reduced gradient, and to tolerances derived from it for the updated weights:
+#   SGD (linear in g):   |dw| <= lr * bound + 2 ulp(w)
+#   Adam, gradients of one sign per element (no cancellation, so the sum's RELATIVE error is
+#   <= (n-1)*2^-24 and the update moves by < 1e-9):  |dw| <= 3e-8  (a few ulp of |w| <= 0.05)
+def _same_sign_grads(n, numels, step):
+    out = []
+    pat = torch.randn(sum(numels), generator=torch.Generator().manual_seed(77)).sign()
+    for r in range(n):
+        g = torch.Generator().manual_seed(4321 + 1000 * r + 100000 * step)
+        out.append((pat * (0.5 + torch.randn(sum(numels), generator=g).abs()) * 1e-3).numpy())
+    return out
+
+
+def _flat(plan, lay, numels, which, dev=0):
+    buf = plan.tensor(dev, which).cpu().numpy()
+    return np.concatenate([buf[lay.tensor_offset(k):lay.tensor_offset(k) + m] for k, m in enumerate(numels)])
+
+
+def _path_b_checks(plan, lay, n, numels, local_devs, ops, sync):
+    """Shared by the local and the rank-context tests.  ops.put(list_of_host_arrays) packs
+    every local rank's gradient, ops.allreduce()/load(w)/step(opt, h) issue the call for every
+    local rank; sync() waits for the device(s)."""
+    N = sum(numels)
+    assert plan.path == "multicast"
+    # (1) all-reduce on cancellation-stress data: order-free bound, every element
+    hg = host_grads(n, numels, 0)
+    ops.put(hg)
+    ops.allreduce()
+    sync()
+    ref = oracle.addn(hg).astype(np.float64)
+    bound = (n - 1) * 2.0 ** -24 * np.sum(np.abs(np.stack(hg)), axis=0) + 1e-30
+    for dev in local_devs:
+        got = _flat(plan, lay, numels, b200dp.BUF_REDUCED, dev).astype(np.float64)
+        assert np.all(np.abs(got - ref) <= bound), "all-reduce outside the order-free bound"
+    # (2) fused SGD step on the same data: linear error bound
+    w0 = ((torch.rand(N, generator=torch.Generator().manual_seed(42)) - 0.5) * 0.1).numpy()
+    ops.load(w0)
+    ops.put(hg)
+    lr = 0.01
+    ops.step("sgdm", b200dp.sgdm_hyper(lr=lr, momentum=0.9))
+    sync()
+    w_ref, a_ref = w0.copy(), np.zeros(N, F)
+    oracle.sgdm_(w_ref, a_ref, oracle.addn(hg), lr=lr, mu=0.9)
+    for dev in local_devs:
+        got = _flat(plan, lay, numels, b200dp.BUF_WEIGHTS, dev)
+        assert np.all(np.abs(got.astype(np.float64) - w_ref) <= lr * bound + 2 * np.spacing(np.abs(w_ref).astype(F)))
+    # (3) fused Adam, two steps, same-sign gradients: |dw| <= 3e-8
+    for dev in local_devs:   # the SGD step above left its accumulator in the state shard
+        plan.tensor(dev, b200dp.BUF_STATE0).zero_()
+        plan.tensor(dev, b200dp.BUF_STATE1).zero_()
+    sync()
+    ops.load(w0)
+    w_ref, m_ref, v_ref = w0.copy(), np.zeros(N, F), np.zeros(N, F)
+    for s in range(2):
+        sg = _same_sign_grads(n, numels, s)
+        ops.put(sg)
+        ops.step("adam", b200dp.adam_hyper(step=s + 1))
+        oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(sg), step=s + 1)
+    sync()
+    for dev in local_devs:
+        got = _flat(plan, lay, numels, b200dp.BUF_WEIGHTS, dev)
+        assert np.max(np.abs(got - w_ref)) <= 3e-8
+
+
+class _Ops:
+    pass
+
+
+@needs2
+def test_path_b_multicast_local_context():
+    n = min(NGPU, 8)
+    numels = b200dp.resnet50_numels()
+    ctx = b200dp.Context.local(list(range(n)))
+    ctx.set_timeout(5.0)
+    lay = b200dp.Layout(numels, nranks=n)
+    plan = b200dp.Plan(ctx, lay)
+    plan.enable_multicast()
+
+    def each(fn):
+        for r in range(n):
+            with torch.cuda.device(r):
+                fn(r)
+
+    ops = _Ops()
+    ops.put = lambda hg: each(lambda r: plan.pack(r, views(torch.from_numpy(hg[r]).cuda(r), numels)))
+    ops.allreduce = lambda: each(lambda r: plan.allreduce(r))
+    ops.load = lambda w: each(lambda r: plan.load_weights(r, views(torch.from_numpy(w).cuda(r), numels)))
+    ops.step = lambda opt, h: each(lambda r: plan.step(r, opt, h))
+
+    def sync():
+        for r in range(n):
+            torch.cuda.synchronize(r)
+
+    _path_b_checks(plan, lay, n, numels, list(range(n)), ops, sync)
+    each(lambda r: plan.check(r))
+
+
+def _rank_worker_mc(rank, n, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=n, device_id=torch.device("cuda", rank))
+    try:
+        numels = b200dp.resnet50_numels()
+        ctx = b200dp.Context.rank(rank, n, rank)
+        ctx.set_timeout(5.0)
+        lay = b200dp.Layout(numels, nranks=n)
+        plan = b200dp.Plan(ctx, lay)
+        plan.exchange("m-%d" % port)
+        plan.enable_multicast("m-%d" % port)
+        dist.barrier()
+        ops = _Ops()
+        ops.put = lambda hg: plan.pack(0, views(torch.from_numpy(hg[rank]).cuda(), numels))
+        ops.allreduce = lambda: plan.allreduce(0)
+        ops.load = lambda w: plan.load_weights(0, views(torch.from_numpy(w).cuda(), numels))
+        ops.step = lambda opt, h: plan.step(0, opt, h)
+        _path_b_checks(plan, lay, n, numels, [0], ops, torch.cuda.synchronize)
+        plan.check(0)
+        dist.barrier()
+        q.put((rank, ""))
+    except Exception:
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+def test_path_b_multicast_rank_contexts():
+    import torch.multiprocessing as mp
+    n = min(NGPU, 8)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank_worker_mc, args=(r, n, port, q)) for r in range(n)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(n)]
+    for p in procs:
+        p.join(60)
+    for rank, err in sorted(results):
+        assert not err, "rank %d:\n%s" % (rank, err)

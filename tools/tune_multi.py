@@ -1,0 +1,105 @@
+"""Single-process sweep of the collective kernels' launch geometry over 2/4/8 GPUs of one box
+(local context = MirroredStrategy's shape).  Developer tool; prints one line per config.
+Times are CUDA-event device times, max over ranks, every launch queued behind a device-side
+sleep so host launch overhead is excluded."""
+import itertools
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import b200dp  # noqa: E402
+
+S = 4 * b200dp.NUM_ELEMENTS
+
+
+def views(flat, numels):
+    out, o = [], 0
+    for k in numels:
+        out.append(flat[o:o + k])
+        o += k
+    return out
+
+
+def time_all(n, fn, reps=20):
+    for _ in range(3):
+        for r in range(n):
+            with torch.cuda.device(r):
+                fn(r)
+    for r in range(n):
+        torch.cuda.synchronize(r)
+    ev = []
+    for r in range(n):
+        with torch.cuda.device(r):
+            torch.cuda._sleep(int(4e7))
+            e0 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ev.append([e0, None])
+    for _ in range(reps):
+        for r in range(n):
+            with torch.cuda.device(r):
+                fn(r)
+    for r in range(n):
+        with torch.cuda.device(r):
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            ev[r][1] = e1
+    for r in range(n):
+        torch.cuda.synchronize(r)
+    return max(e0.elapsed_time(e1) for e0, e1 in ev) / reps * 1e3   # us
+
+
+def main():
+    ndev = torch.cuda.device_count()
+    numels = b200dp.resnet50_numels()
+    results = []
+    for n in [x for x in (2, 4, 8) if x <= ndev]:
+        ctx = b200dp.Context.local(list(range(n)))
+        ctx.set_timeout(5.0)
+        lay = b200dp.Layout(numels, nranks=n)
+        plan = b200dp.Plan(ctx, lay)
+        plan.enable_multicast()
+        for r in range(n):
+            with torch.cuda.device(r):
+                g = torch.randn(sum(numels), device="cuda:%d" % r) * 1e-3
+                plan.pack(r, views(g, numels))
+                plan.tensor(r, b200dp.BUF_WEIGHTS).uniform_(-0.05, 0.05)
+        t = [0]
+
+        def step(r):
+            if r == 0:
+                t[0] += 1
+            plan.step(r, "adam", b200dp.adam_hyper(step=t[0] + 1))
+
+        def allreduce(r):
+            plan.allreduce(r, postscale=1.0 / n)
+
+        configs = [("multicast", dict(mc_unroll=u, mc_grid_cap=c)) for u, c in itertools.product((1, 2, 4), (37, 74, 148, 296))]
+        configs += [("peer", dict(peer_unroll=u, grid_cap=c)) for u, c in itertools.product((1, 2), (74, 148, 296, 592))]
+        for path, knobs in configs:
+            plan.set_path(path)
+            plan.set_tuning(**knobs)
+            us_step = time_all(n, step)
+            us_ar = time_all(n, allreduce)
+            for r in range(n):
+                with torch.cuda.device(r):
+                    plan.check(r)
+            row = {"n": n, "path": path, **knobs, "step_us": round(us_step, 1), "allreduce_us": round(us_ar, 1),
+                   "step_busbw": round(S / us_step * 2 * (n - 1) / n / 1e3, 1)}
+            results.append(row)
+            print(json.dumps(row), flush=True)
+        del plan, ctx
+    best = {}
+    for row in results:
+        k = (row["n"], row["path"])
+        if k not in best or row["step_us"] < best[k]["step_us"]:
+            best[k] = row
+    print("BEST")
+    for k in sorted(best):
+        print(json.dumps(best[k]))
+
+
+if __name__ == "__main__":
+    main()
