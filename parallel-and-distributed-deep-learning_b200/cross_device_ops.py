@@ -1,0 +1,189 @@
+"""B200CrossDeviceOps -- the tf.distribute.CrossDeviceOps plug-in point, over libb200dp.so.
+
+Reference boundary: ``strategy = tf.distribute.MirroredStrategy()``
+(imagenet-resnet50-mirror.py:21) becomes
+``MirroredStrategy(cross_device_ops=B200CrossDeviceOps())``; under ``model.fit`` (:81) Keras
+then calls ``batch_reduce(ReduceOp.SUM, [(PerReplica grad_k, variable_k)] * 214)`` once per
+step [upstream tensorflow/python/distribute/cross_device_ops.py].
+
+Two classes share one engine:
+  * ``B200CrossDeviceOps``      -- executed and tested here: same method names, argument meaning
+    and error behaviour, with per-replica values given as lists of torch CUDA tensors (one per
+    replica) because TensorFlow is not installed on this image.
+  * ``make_tf_cross_device_ops()`` -- returns the real ``tf.distribute.CrossDeviceOps`` subclass
+    when TensorFlow is importable (tensors cross via DLPack inside a ``tf.py_function``, since
+    the hook runs while the step function is being traced).  Written against the upstream API,
+    **unexecuted on this image**.
+"""
+import enum
+
+from . import api
+from ._lib import BUF_REDUCED
+
+
+class ReduceOp(enum.Enum):
+    """tf.distribute.ReduceOp"""
+    SUM = "SUM"
+    MEAN = "MEAN"
+
+
+class CommunicationOptions:
+    """tf.distribute.experimental.CommunicationOptions (imagenet-resnet50-multiworkers.py:20-21):
+    bytes_per_pack maps to the bucket size of the layout; 0 = one pack, as upstream."""
+
+    def __init__(self, bytes_per_pack=0, timeout_seconds=None, implementation=None):
+        if bytes_per_pack < 0:
+            raise ValueError("Argument `bytes_per_pack` must be >=0, Received %d." % bytes_per_pack)
+        self.bytes_per_pack = bytes_per_pack
+        self.timeout_seconds = timeout_seconds
+        self.implementation = implementation
+
+
+class _Engine:
+    """Caches one plan per (tensor sizes, devices, bucket size) and runs pack -> allreduce -> unpack."""
+
+    def __init__(self, wire="f32"):
+        self.wire = wire
+        self._plans = {}
+
+    def plan_for(self, numels, devices, bucket_bytes):
+        key = (tuple(numels), tuple(devices), int(bucket_bytes))
+        if key not in self._plans:
+            ctx = api.Context.local(devices)
+            lay = api.Layout(numels, nranks=len(devices), wire=self.wire, bucket_bytes=bucket_bytes)
+            self._plans[key] = (ctx, lay, api.Plan(ctx, lay))
+        return self._plans[key][2]
+
+    def all_reduce(self, per_replica, reduce_op, bucket_bytes):
+        """per_replica[r][k] = tensor k on replica r.  Returns the same structure, reduced."""
+        import torch
+        n = len(per_replica)
+        numels = [t.numel() for t in per_replica[0]]
+        devices = [ts[0].device.index if ts else 0 for ts in per_replica]
+        plan = self.plan_for(numels, devices, bucket_bytes)
+        post = 1.0 / n if reduce_op == ReduceOp.MEAN else 1.0
+        outs = []
+        for r in range(n):
+            with torch.cuda.device(devices[r]):
+                plan.pack(r, [t.contiguous() for t in per_replica[r]])
+        for r in range(n):
+            with torch.cuda.device(devices[r]):
+                plan.allreduce(r, postscale=post)
+        for r in range(n):
+            with torch.cuda.device(devices[r]):
+                o = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in per_replica[r]]
+                plan.unpack(r, o, which=BUF_REDUCED)
+                outs.append(o)
+        return outs
+
+
+class B200CrossDeviceOps:
+    """Drop-in for tf.distribute.CrossDeviceOps on the gradient path (torch-tensor flavour).
+
+    A *per-replica value* is a list with one tensor per replica (``PerReplica.values``); the
+    result is a list with one tensor per destination replica (``Mirrored.values``), every
+    entry holding the same reduced value.
+    """
+
+    def __init__(self, wire="f32"):
+        self._engine = _Engine(wire)
+
+    # -- public API, as upstream ---------------------------------------------------------
+    def reduce(self, reduce_op, per_replica_value, destinations=None, options=None):
+        return self.batch_reduce(reduce_op, [(per_replica_value, destinations)], options)[0]
+
+    def batch_reduce(self, reduce_op, value_destination_pairs, options=None):
+        if not isinstance(reduce_op, ReduceOp):
+            reduce_op = ReduceOp(str(reduce_op).split(".")[-1].upper())
+        if options is None:
+            options = CommunicationOptions()
+        self._validate(value_destination_pairs)
+        return self.batch_reduce_implementation(reduce_op, value_destination_pairs, options)
+
+    def broadcast(self, tensor, destinations):
+        return [tensor.to("cuda:%d" % d) for d in destinations]
+
+    # -- implementation hooks, as upstream ------------------------------------------------
+    def reduce_implementation(self, reduce_op, per_replica_value, destinations, options):
+        return self.batch_reduce_implementation(reduce_op, [(per_replica_value, destinations)], options)[0]
+
+    def batch_reduce_implementation(self, reduce_op, value_destination_pairs, options):
+        values = [v for v, _ in value_destination_pairs]
+        if not values:
+            return []
+        n = len(values[0])
+        per_replica = [[v[r] for v in values] for r in range(n)]
+        reduced = self._engine.all_reduce(per_replica, reduce_op, options.bytes_per_pack)
+        return [[reduced[r][k] for r in range(n)] for k in range(len(values))]
+
+    @staticmethod
+    def _validate(pairs):
+        n = None
+        for k, (value, _dest) in enumerate(pairs):
+            if not isinstance(value, (list, tuple)) or not value:
+                raise ValueError("value %d is not a per-replica value (a non-empty list of tensors)" % k)
+            if n is None:
+                n = len(value)
+            if len(value) != n:
+                raise ValueError("value %d has %d replicas, expected %d" % (k, len(value), n))
+            shape = tuple(value[0].shape)
+            for t in value:
+                if tuple(t.shape) != shape:
+                    raise ValueError("value %d: replicas disagree on shape (%s vs %s)" % (k, tuple(t.shape), shape))
+                if not t.is_cuda:
+                    raise ValueError("value %d lives on %s; this library has no CPU path" % (k, t.device))
+                if str(t.dtype) != "torch.float32":
+                    raise ValueError("value %d has dtype %s; gradients must be float32" % (k, t.dtype))
+        devs = [t.device for t in pairs[0][0]] if pairs else []
+        for k, (value, _dest) in enumerate(pairs):
+            if [t.device for t in value] != devs:
+                raise ValueError("value %d is placed on different devices than value 0" % k)
+
+
+def make_tf_cross_device_ops(wire="f32"):
+    """The tf.distribute.CrossDeviceOps subclass itself.  UNEXECUTED on this image (no
+    TensorFlow); raises ImportError here.  Stream ordering between TensorFlow's compute stream
+    and the py_function is the known open item (SURVEY.md 7 "hard parts"): a compiled OpKernel
+    over the same C ABI is the proper fix once TF headers exist."""
+    try:
+        import tensorflow as tf
+    except ImportError as e:  # pragma: no cover - TF absent on this image
+        raise ImportError("TensorFlow is not installed: the TF-facing B200CrossDeviceOps cannot be built here. "
+                          "Use b200dp.cross_device_ops.B200CrossDeviceOps (torch tensors) or bind "
+                          "include/b200dp.h as INTEGRATION.md section 2 shows.") from e
+
+    import torch
+    from torch.utils import dlpack as torch_dlpack
+
+    engine = _Engine(wire)
+
+    class TFB200CrossDeviceOps(tf.distribute.CrossDeviceOps):  # pragma: no cover
+        def reduce_implementation(self, reduce_op, per_replica_value, destinations, options):
+            return self.batch_reduce_implementation(reduce_op, [(per_replica_value, destinations)], options)[0]
+
+        def batch_reduce_implementation(self, reduce_op, value_destination_pairs, options):
+            values = [v for v, _ in value_destination_pairs]
+            n = len(values[0].values)
+            flat_in = [t for v in values for t in v.values]           # K * n tensors, k-major
+            op = ReduceOp.MEAN if reduce_op == tf.distribute.ReduceOp.MEAN else ReduceOp.SUM
+
+            def run(*tensors):
+                per_replica = [[torch_dlpack.from_dlpack(tf.experimental.dlpack.to_dlpack(tensors[k * n + r]))
+                                for k in range(len(values))] for r in range(n)]
+                reduced = engine.all_reduce(per_replica, op, options.bytes_per_pack if options else 0)
+                torch.cuda.synchronize()
+                return [tf.experimental.dlpack.from_dlpack(torch_dlpack.to_dlpack(reduced[r][k]))
+                        for k in range(len(values)) for r in range(n)]
+
+            outs = tf.py_function(run, flat_in, [t.dtype for t in flat_in])
+            result = []
+            for k, v in enumerate(values):
+                per_dev = []
+                for r, src in enumerate(v.values):
+                    with tf.device(src.device):
+                        per_dev.append(tf.reshape(tf.identity(outs[k * n + r]), src.shape))
+                result.append(tf.distribute.DistributedValues(per_dev) if hasattr(tf.distribute, "DistributedValues")
+                              else per_dev)
+            return result
+
+    return TFB200CrossDeviceOps()

@@ -1,0 +1,81 @@
+"""The reference-shaped glue on a GPU: B200CrossDeviceOps.batch_reduce (MirroredStrategy's
+hook) and the Horovod-shaped module, against the oracle (bit-exact: peer path)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+import b200dp  # noqa: E402
+import oracle  # noqa: E402
+from b200dp import cross_device_ops as cdo  # noqa: E402
+
+F = np.float32
+
+
+def test_batch_reduce_sum_and_mean_two_replicas_on_one_gpu():
+    """214 ResNet-50-shaped gradients, 2 replicas (emulated on cuda:0), SUM and MEAN."""
+    shapes = [s for _, s in b200dp.resnet50_trainable_variables()]
+    g = torch.Generator(device="cuda").manual_seed(1)
+    vals = [[torch.randn(s, generator=g, device="cuda") * 1e-2 for _ in range(2)] for s in shapes]
+    ops = cdo.B200CrossDeviceOps()
+    for op in (cdo.ReduceOp.SUM, cdo.ReduceOp.MEAN):
+        out = ops.batch_reduce(op, [(v, None) for v in vals], cdo.CommunicationOptions(bytes_per_pack=8 << 20))
+        torch.cuda.synchronize()
+        assert len(out) == len(vals) and all(len(o) == 2 for o in out)
+        for k in (0, 1, 57, 100, 212, 213):
+            ref = oracle.addn([vals[k][0].cpu().numpy().ravel(), vals[k][1].cpu().numpy().ravel()])
+            if op == cdo.ReduceOp.MEAN:
+                ref = oracle.div_n(ref, 2)
+            for r in range(2):
+                assert out[k][r].shape == vals[k][r].shape
+                assert np.array_equal(out[k][r].cpu().numpy().ravel().view(np.uint32), ref.view(np.uint32))
+
+
+def test_reduce_single_value():
+    v = [torch.full((1000,), 1.5, device="cuda"), torch.full((1000,), 2.25, device="cuda")]
+    out = cdo.B200CrossDeviceOps().reduce(cdo.ReduceOp.SUM, v)
+    assert torch.all(out[0] == 3.75) and torch.all(out[1] == 3.75)
+
+
+def test_hvd_single_process_surface():
+    from b200dp import hvd
+    hvd.shutdown()
+    hvd.init()
+    assert (hvd.rank(), hvd.size(), hvd.local_rank()) == (0, 1, 0)
+    x = torch.randn(12345, device="cuda")
+    assert torch.equal(hvd.allreduce(x), x)                       # Average over one rank
+    assert torch.equal(hvd.allreduce(x, op=hvd.Sum, postscale_factor=0.5), x * 0.5)
+    with pytest.raises(ValueError):
+        hvd.allreduce(x, average=True, op=hvd.Sum)
+    # DistributedOptimizer(size 1) == the wrapped optimizer
+    p1 = torch.nn.Parameter(torch.ones(100, device="cuda"))
+    p2 = torch.nn.Parameter(torch.ones(100, device="cuda"))
+    o1 = hvd.DistributedOptimizer(torch.optim.SGD([p1], lr=0.1))
+    o2 = torch.optim.SGD([p2], lr=0.1)
+    p1.grad = torch.full((100,), 0.5, device="cuda")
+    p2.grad = torch.full((100,), 0.5, device="cuda")
+    o1.step()
+    o2.step()
+    assert torch.equal(p1, p2)
+
+
+def test_hvd_fused_adam_matches_oracle():
+    from b200dp import hvd
+    hvd.shutdown()
+    hvd.init()
+    rng = np.random.default_rng(3)
+    shapes = [(64, 3, 7, 7), (64,), (1000, 2048), (1000,)]
+    params = [torch.nn.Parameter(torch.from_numpy(rng.standard_normal(s).astype(F) * 0.05).cuda()) for s in shapes]
+    w = np.concatenate([p.detach().cpu().numpy().ravel() for p in params])
+    m, v = np.zeros_like(w), np.zeros_like(w)
+    opt = hvd.FusedDistributedAdam(params, lr=1e-3)
+    for step in (1, 2, 3):
+        gs = [rng.standard_normal(s).astype(F) * 1e-2 for s in shapes]
+        for p, g in zip(params, gs):
+            p.grad = torch.from_numpy(g).cuda()
+        opt.step()
+        oracle.adam_(w, m, v, np.concatenate([g.ravel() for g in gs]), lr=1e-3, step=step)
+    torch.cuda.synchronize()
+    got = np.concatenate([p.detach().cpu().numpy().ravel() for p in params])
+    assert np.array_equal(got.view(np.uint32), w.view(np.uint32))

@@ -313,3 +313,71 @@ def test_path_b_multicast_rank_contexts():
         p.join(60)
     for rank, err in sorted(results):
         assert not err, "rank %d:\n%s" % (rank, err)
+
+
+# ------------------------------------------------------------------ hvd-shaped module, n ranks
+def _hvd_worker(rank, n, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n),
+                      LOCAL_RANK=str(rank))
+    try:
+        from b200dp import hvd
+        hvd.init()
+        assert (hvd.rank(), hvd.size(), hvd.local_rank()) == (rank, n, rank)
+        shapes = [(64, 3, 7, 7), (64,), (1000, 2048), (1000,), (3,)]
+        numels = [int(np.prod(s)) for s in shapes]
+        hg = host_grads(n, numels, 3)
+        mine = [t.view(s) for t, s in zip(views(torch.from_numpy(hg[rank]).cuda(), numels), shapes)]
+        # hvd.allreduce(op=Average) on a fused group == oracle sum * float(1/n)
+        outs = hvd.grouped_allreduce(mine, op=hvd.Average)
+        torch.cuda.synchronize()
+        ref = oracle.scale(oracle.addn(hg), 1.0 / n)
+        got = np.concatenate([o.cpu().numpy().ravel() for o in outs])
+        ok_avg = bool(np.array_equal(bits(got), bits(ref)))
+        # fused Adam with Average
+        rng = np.random.default_rng(5)
+        w0 = [rng.standard_normal(s).astype(F) * 0.05 for s in shapes]
+        params = [torch.nn.Parameter(torch.from_numpy(x).cuda()) for x in w0]
+        hvd.broadcast_parameters(params, root_rank=0)
+        opt = hvd.FusedDistributedAdam(params, lr=1e-3)
+        w = np.concatenate([x.ravel() for x in w0])
+        m, v = np.zeros_like(w), np.zeros_like(w)
+        for step in (1, 2):
+            hg = host_grads(n, numels, 10 + step)
+            for p, g, s in zip(params, views(torch.from_numpy(hg[rank]).cuda(), numels), shapes):
+                p.grad = g.view(s)
+            opt.step()
+            oracle.adam_(w, m, v, oracle.scale(oracle.addn(hg), 1.0 / n), lr=1e-3, step=step)
+        torch.cuda.synchronize()
+        got = np.concatenate([p.detach().cpu().numpy().ravel() for p in params])
+        ok_adam = bool(np.array_equal(bits(got), bits(w)))
+        import torch.distributed as dist
+        dist.barrier()
+        q.put((rank, ok_avg, ok_adam, ""))
+        dist.destroy_process_group()
+    except Exception:
+        import traceback
+        q.put((rank, False, False, traceback.format_exc()))
+
+
+@needs2
+def test_hvd_module_one_process_per_gpu():
+    import torch.multiprocessing as mp
+    n = min(NGPU, 8)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_hvd_worker, args=(r, n, port, q)) for r in range(n)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(n)]
+    for p in procs:
+        p.join(60)
+    for rank, ok_avg, ok_adam, err in sorted(results):
+        assert not err, err
+        assert ok_avg, "rank %d: hvd Average differs from the oracle" % rank
+        assert ok_adam, "rank %d: fused Adam differs from the oracle" % rank
