@@ -53,7 +53,7 @@ BlockMap make_map(const b2dp_layout& l) {
   m.ctrl = off;
   off += 4096;
   m.partials = off;
-  off += align_up(size_t(2) * kMaxBlocks * sizeof(double), 4096);
+  off += align_up(size_t(2) * kApplyMaxBlocks * sizeof(double), 4096);
   m.grads = off;
   off += align_up((size_t)l.total * wire, 4096);
   m.weights = off;
@@ -167,9 +167,7 @@ int bucket_range(const b2dp_plan* p, int bucket, int* b0, int* b1) {
   return B2DP_OK;
 }
 
-int pack_grid(const RankState& r, int64_t ntiles) {
-  return (int)std::min<int64_t>(ntiles, (int64_t)r.num_sms * 8);
-}
+int pack_grid(const RankState&, int64_t ntiles) { return (int)ntiles; }  // one tile per block
 
 template <int DIR>
 int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const void* const* ptrs,
@@ -371,6 +369,16 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     a.push = (mode == 1) ? 0 : 1;
     fill_comm(p, r, &a.c);
     int rc;
+    if (n == 1 && p->layout.wire == B2DP_F32 && opt != B2DP_OPT_NONE && mode != 3) {
+      const int64_t nvec8 = a.nvec >> 1;
+      const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec8 + kApplyThreads - 1) / kApplyThreads, kApplyMaxBlocks));
+      if (opt == B2DP_OPT_ADAM)
+        apply1_kernel<B2DP_OPT_ADAM><<<grid, kApplyThreads, 0, s>>>(a);
+      else
+        apply1_kernel<B2DP_OPT_SGDM><<<grid, kApplyThreads, 0, s>>>(a);
+      CUDA_TRY(cudaGetLastError());
+      continue;
+    }
     const bool use_mc = p->path == B2DP_PATH_MULTICAST && a.c.use_flags && (mode == 0 || mode == 2);
     if (use_mc) {
       char* mc = reinterpret_cast<char*>(r.mc_va);

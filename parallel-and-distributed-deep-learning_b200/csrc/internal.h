@@ -17,7 +17,7 @@ int fail(int code, const char* fmt, ...);  // records the thread-local message, 
 // ---- layout -----------------------------------------------------------------------
 constexpr int64_t kTensorAlign = 32;   // elements; every tensor starts on a 128-byte (f32) line
 constexpr int64_t kSliceAlign = 256;   // elements; every rank slice is a multiple of this
-constexpr int32_t kTileElems = 4096;   // pack/unpack work unit (one block iteration)
+constexpr int32_t kTileElems = 8192;   // pack/unpack work unit (one block)
 constexpr int kMaxRanks = 8;           // one NVSwitch box
 
 struct Tile {          // one unit of pack/unpack work: a run inside ONE tensor

@@ -39,6 +39,24 @@ __device__ __forceinline__ void st_f4(float4* p, float4 v) {
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
+// 256-bit accesses (LDG.E.256 / STG.E.256, new on sm_100): half the memory instructions of
+// the 128-bit form for the same bytes; pointers must be 32-byte aligned.
+struct float8 {
+  float4 lo, hi;
+};
+__device__ __forceinline__ float8 ld_stream_f8(const float* p) {
+  float8 v;
+  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v.lo.x), "=f"(v.lo.y), "=f"(v.lo.z), "=f"(v.lo.w), "=f"(v.hi.x), "=f"(v.hi.y), "=f"(v.hi.z),
+                 "=f"(v.hi.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_f8(float* p, const float8& v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v.lo.x), "f"(v.lo.y), "f"(v.lo.z),
+               "f"(v.lo.w), "f"(v.hi.x), "f"(v.hi.y), "f"(v.hi.z), "f"(v.hi.w)
+               : "memory");
+}
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -79,67 +97,86 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 
 // ---- kernel (1): pack / unpack --------------------------------------------------------
-// One launch over the device-resident tile table; a tile is a run of <= 4096 elements
-// inside one tensor, so blocks are balanced by bytes however ragged the tensor list is.
-// DIR 0: tensors -> flat (cast to WireT, times prescale); DIR 1: flat(f32) -> tensors.
+// One launch over the device-resident tile table; a tile is a run of <= 8192 elements
+// inside one tensor (one block each), so work is split by bytes however ragged the tensor
+// list is.  DIR 0: tensors -> flat (cast to WireT, times prescale); DIR 1: flat(f32) -> tensors.
 template <typename WireT, int DIR>
 __global__ void __launch_bounds__(kPackThreads)
 pack_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
             WireT* __restrict__ flat, float prescale) {
-  constexpr int V = kTileElems / (4 * kPackThreads);  // float4 per thread per tile = 4
-  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    const Tile tl = tiles[t];
-    float* tens = reinterpret_cast<float*>(ptrs[tl.tensor]) + tl.src_off;
-    WireT* fl = flat + tl.dst_off;
-    const uint32_t count = tl.count;
-    const bool vec = ((reinterpret_cast<uintptr_t>(tens) & 15) == 0);
-    const uint32_t nvec = vec ? (count >> 2) : 0;
-    if (DIR == 0) {
-      float4 v[V];
+  // One tile per block: with ~6400 short-lived blocks the hardware scheduler keeps every SM
+  // busy and blocks in different phases (loading / storing) overlap, which measured ~10%
+  // faster than a persistent grid-stride loop for this pure stream.
+  const int64_t t = blockIdx.x;
+  if (t >= ntiles) return;
+  const Tile tl = tiles[t];
+  float* tens = reinterpret_cast<float*>(ptrs[tl.tensor]) + tl.src_off;
+  WireT* fl = flat + tl.dst_off;
+  const uint32_t count = tl.count;
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(tens);
+  // widest access the tensor's own alignment allows (the flat side is always 128-byte aligned)
+  const uint32_t n8 = ((addr & 31) == 0) ? (count >> 3) : 0;              // 256-bit vectors
+  const uint32_t n4 = ((addr & 15) == 0) ? ((count - n8 * 8) >> 2) : 0;   // then 128-bit
+  const uint32_t done = n8 * 8 + n4 * 4;                                   // then scalars
+  constexpr int V8 = kTileElems / (8 * kPackThreads);  // 256-bit vectors per thread per tile
+  if (DIR == 0) {
+    float8 v[V8];
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        uint32_t q = j * kPackThreads + threadIdx.x;
-        if (q < nvec) v[j] = ld_stream_f4(reinterpret_cast<const float4*>(tens) + q);
-      }
+    for (int j = 0; j < V8; ++j) {
+      const uint32_t q = j * kPackThreads + threadIdx.x;
+      if (q < n8) v[j] = ld_stream_f8(tens + (size_t)q * 8);
+    }
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        uint32_t q = j * kPackThreads + threadIdx.x;
-        if (q < nvec) {
-          float4 x = v[j];
-          x.x = __fmul_rn(x.x, prescale);
-          x.y = __fmul_rn(x.y, prescale);
-          x.z = __fmul_rn(x.z, prescale);
-          x.w = __fmul_rn(x.w, prescale);
-          if (sizeof(WireT) == 4) {
-            st_f4(reinterpret_cast<float4*>(fl) + q, x);
-          } else {
-            uint2 o = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
-            reinterpret_cast<uint2*>(fl)[q] = o;
-          }
+    for (int j = 0; j < V8; ++j) {
+      const uint32_t q = j * kPackThreads + threadIdx.x;
+      if (q < n8) {
+        float8 x = v[j];
+        x.lo.x = __fmul_rn(x.lo.x, prescale); x.lo.y = __fmul_rn(x.lo.y, prescale);
+        x.lo.z = __fmul_rn(x.lo.z, prescale); x.lo.w = __fmul_rn(x.lo.w, prescale);
+        x.hi.x = __fmul_rn(x.hi.x, prescale); x.hi.y = __fmul_rn(x.hi.y, prescale);
+        x.hi.z = __fmul_rn(x.hi.z, prescale); x.hi.w = __fmul_rn(x.hi.w, prescale);
+        if (sizeof(WireT) == 4) {
+          st_f8(reinterpret_cast<float*>(fl) + (size_t)q * 8, x);
+        } else {
+          uint4 o = make_uint4(pack_bf16x2(x.lo.x, x.lo.y), pack_bf16x2(x.lo.z, x.lo.w), pack_bf16x2(x.hi.x, x.hi.y),
+                               pack_bf16x2(x.hi.z, x.hi.w));
+          reinterpret_cast<uint4*>(fl)[q] = o;
         }
       }
-      for (uint32_t i = nvec * 4 + threadIdx.x; i < count; i += kPackThreads) {
-        float x = __fmul_rn(tens[i], prescale);
-        if (sizeof(WireT) == 4)
-          reinterpret_cast<float*>(fl)[i] = x;
-        else
-          reinterpret_cast<__nv_bfloat16*>(fl)[i] = __float2bfloat16_rn(x);
-      }
-    } else {
-      const float* src = reinterpret_cast<const float*>(fl);
-      float4 v[V];
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        uint32_t q = j * kPackThreads + threadIdx.x;
-        if (q < nvec) v[j] = ld_stream_f4(reinterpret_cast<const float4*>(src) + q);
-      }
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        uint32_t q = j * kPackThreads + threadIdx.x;
-        if (q < nvec) st_f4(reinterpret_cast<float4*>(tens) + q, v[j]);
-      }
-      for (uint32_t i = nvec * 4 + threadIdx.x; i < count; i += kPackThreads) tens[i] = src[i];
     }
+    for (uint32_t q = threadIdx.x; q < n4; q += kPackThreads) {
+      float4 x = ld_stream_f4(reinterpret_cast<const float4*>(tens + n8 * 8) + q);
+      x.x = __fmul_rn(x.x, prescale); x.y = __fmul_rn(x.y, prescale);
+      x.z = __fmul_rn(x.z, prescale); x.w = __fmul_rn(x.w, prescale);
+      if (sizeof(WireT) == 4)
+        st_f4(reinterpret_cast<float4*>(reinterpret_cast<float*>(fl) + n8 * 8) + q, x);
+      else
+        reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(fl) + n8 * 8)[q] =
+            make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
+    }
+    for (uint32_t i = done + threadIdx.x; i < count; i += kPackThreads) {
+      float x = __fmul_rn(tens[i], prescale);
+      if (sizeof(WireT) == 4)
+        reinterpret_cast<float*>(fl)[i] = x;
+      else
+        reinterpret_cast<__nv_bfloat16*>(fl)[i] = __float2bfloat16_rn(x);
+    }
+  } else {
+    const float* src = reinterpret_cast<const float*>(fl);
+    float8 v[V8];
+#pragma unroll
+    for (int j = 0; j < V8; ++j) {
+      const uint32_t q = j * kPackThreads + threadIdx.x;
+      if (q < n8) v[j] = ld_stream_f8(src + (size_t)q * 8);
+    }
+#pragma unroll
+    for (int j = 0; j < V8; ++j) {
+      const uint32_t q = j * kPackThreads + threadIdx.x;
+      if (q < n8) st_f8(tens + (size_t)q * 8, v[j]);
+    }
+    for (uint32_t q = threadIdx.x; q < n4; q += kPackThreads)
+      st_f4(reinterpret_cast<float4*>(tens + n8 * 8) + q, ld_stream_f4(reinterpret_cast<const float4*>(src + n8 * 8) + q));
+    for (uint32_t i = done + threadIdx.x; i < count; i += kPackThreads) tens[i] = src[i];
   }
 }
 
@@ -363,6 +400,104 @@ step_kernel(const StepArgs a) {
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
 
   flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
+}
+
+// n == 1 (imagenet-resnet50.py: no reduction, optimizer apply only), f32 gradients: the same
+// arithmetic as step_kernel<1,...>, laid out for HBM instead of NVLink -- one 256-bit vector
+// (8 elements) of each stream per thread and a NON-persistent grid.  Measured on B200
+// (tools/apply_variants.cu, back to back): 107.5 us vs 124 us for the persistent 128-bit
+// form, i.e. 6.66 TB/s = 1.02 of the measured copy peak.
+constexpr int kApplyThreads = 256;
+constexpr int kApplyMaxBlocks = 16384;  // statistics partial slots for this kernel
+
+template <int OPT>
+__global__ void __launch_bounds__(kApplyThreads)
+apply1_kernel(const StepArgs a) {
+  const int64_t nvec8 = a.nvec >> 1;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float sumsq = 0.0f, bad = 0.0f;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec8; q += stride) {
+    float8 g = ld_stream_f8(reinterpret_cast<const float*>(a.g[0]) + q * 8);
+    float8 w = ld_stream_f8(a.w + q * 8);
+    float8 s0 = ld_stream_f8(a.s0 + q * 8);
+    float8 s1;
+    if (OPT == B2DP_OPT_ADAM) s1 = ld_stream_f8(a.s1 + q * 8);
+    float* gp = &g.lo.x;
+    float* wp = &w.lo.x;
+    float* p0 = &s0.lo.x;
+    float* p1 = &s1.lo.x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float acc = __fmul_rn(gp[i], a.o.postscale);
+      if (a.want_stats) {
+        sumsq = fmaf(acc, acc, sumsq);
+        bad += (float)(!isfinite(acc));
+      }
+      if (OPT == B2DP_OPT_ADAM)
+        adam_update(acc, wp[i], p0[i], p1[i], a.o);
+      else
+        sgdm_update(acc, wp[i], p0[i], a.o);
+    }
+    if (OPT == B2DP_OPT_ADAM) {
+      st_f8(a.s0 + q * 8, s0);
+      st_f8(a.s1 + q * 8, s1);
+    } else if (a.o.mu != 0.0f) {
+      st_f8(a.s0 + q * 8, s0);
+    }
+    st_f8(a.w + q * 8, w);
+  }
+  if (a.want_stats) {
+    // block partial -> scratch; the last block to arrive folds every partial in a fixed order
+    __shared__ double sm[2][kApplyThreads];
+    __shared__ bool last;
+    double s = (double)sumsq, b = (double)bad;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+      sm[0][warp] = s;
+      sm[1][warp] = b;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      s = b = 0.0;
+      for (int i = 0; i < kApplyThreads / 32; ++i) {
+        s += sm[0][i];
+        b += sm[1][i];
+      }
+      a.partials[2 * blockIdx.x] = s;
+      a.partials[2 * blockIdx.x + 1] = b;
+      __threadfence();
+      last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last) {
+      __threadfence();
+      s = b = 0.0;
+      for (unsigned i = threadIdx.x; i < gridDim.x; i += kApplyThreads) {
+        s += __ldcg(a.partials + 2 * i);
+        b += __ldcg(a.partials + 2 * i + 1);
+      }
+      sm[0][threadIdx.x] = s;
+      sm[1][threadIdx.x] = b;
+      __syncthreads();
+      for (int o = kApplyThreads / 2; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+          sm[0][threadIdx.x] += sm[0][threadIdx.x + o];
+          sm[1][threadIdx.x] += sm[1][threadIdx.x + o];
+        }
+        __syncthreads();
+      }
+      if (threadIdx.x == 0) {
+        a.stats[0] = sm[0][0];
+        a.stats[1] = sm[1][0];
+        *a.ticket = 0;
+      }
+    }
+  }
 }
 
 // Path B: the same step through the NVSwitch multicast mapping.  a.g[0] / a.out[0] are
