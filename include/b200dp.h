@@ -200,6 +200,15 @@ int b2dp_pack(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grad
 int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp_hyper* hyper,
               void* stream);
 
+/* pack + step as one call -- what a binding normally issues once per training step.  With
+ * one rank and an f32 wire (imagenet-resnet50.py:62,67: no reduction, 214 x ResourceApplyAdam)
+ * it is a single kernel that reads each gradient in place through the tile table and never
+ * materialises the bucket (28 instead of 36 bytes of HBM traffic per element); with n > 1 it
+ * is b2dp_pack followed by b2dp_step.  Results are bit-identical to the two-call form. */
+int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads,
+                   int32_t grad_dtype, float prescale, int32_t opt, const b2dp_hyper* hyper,
+                   void* stream);
+
 /* hvd-compatible allreduce: same reduce-scatter + all-gather with no optimizer; the
  * result (sum * postscale, fp32) lands in B2DP_BUF_REDUCED of every rank.  Replaces
  * hvd.allreduce(op=Average|Sum) under hvd.DistributedOptimizer (-hvd.py:101) and

@@ -70,6 +70,8 @@ SIGNATURES = {
     "b2dp_plan_path": (_i32, [_vp]),
     "b2dp_plan_set_tuning": (ctypes.c_int, [_vp, _i32, _i32]),
     "b2dp_pack": (ctypes.c_int, [_vp, _i32, _i32, ctypes.POINTER(_vp), _i32, ctypes.c_float, _vp]),
+    "b2dp_pack_step": (ctypes.c_int, [_vp, _i32, _i32, ctypes.POINTER(_vp), _i32, ctypes.c_float, _i32,
+                                      ctypes.POINTER(Hyper), _vp]),
     "b2dp_step": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(Hyper), _vp]),
     "b2dp_allreduce": (ctypes.c_int, [_vp, _i32, _i32, ctypes.c_float, _vp]),
     "b2dp_reduce_scatter_apply": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(Hyper), _vp]),

@@ -299,6 +299,13 @@ class Plan:
         check(self._L.b2dp_step(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
                                 self._stream(stream, dev)))
 
+    def pack_step(self, dev, grads, opt, hyper, prescale=1.0, bucket=-1, stream=None):
+        """pack + step in one call (one kernel when there is a single rank)."""
+        if not isinstance(grads, ctypes.Array) and len(grads) != self.layout.num_tensors:
+            raise ValueError("pack_step: %d tensors, plan has %d" % (len(grads), self.layout.num_tensors))
+        check(self._L.b2dp_pack_step(self._h, dev, bucket, _ptr_array(grads), F32, prescale, _OPTS[opt],
+                                     ctypes.byref(hyper), self._stream(stream, dev)))
+
     def reduce_scatter_apply(self, dev, opt, hyper, bucket=-1, stream=None):
         check(self._L.b2dp_reduce_scatter_apply(self._h, dev, bucket, _OPTS[opt], ctypes.byref(hyper),
                                                 self._stream(stream, dev)))

@@ -85,6 +85,8 @@ struct RankState {
   char* base[kMaxRanks] = {};  // every rank's block as addressable from this rank's GPU
   bool attached[kMaxRanks] = {};
   Tile* d_tiles = nullptr;
+  TileAbs* d_tiles_abs = nullptr;  // tiles with the gradient pointers resolved (n == 1 fused kernel)
+  bool abs_valid = false;
   PtrTable grads, outs, weights;
   uint32_t epoch = 0;
   int num_sms = 0;
@@ -136,10 +138,12 @@ int check_device(int device) {
   return B2DP_OK;
 }
 
-int sync_table(PtrTable& t, const void* const* ptrs, int K, cudaStream_t s) {
+int sync_table(PtrTable& t, const void* const* ptrs, int K, cudaStream_t s, bool* changed = nullptr) {
+  if (changed) *changed = false;
   if (K == 0) return B2DP_OK;
   if (!t.dev) CUDA_TRY(cudaMalloc(&t.dev, sizeof(void*) * K));
   if ((int)t.host.size() == K && memcmp(t.host.data(), ptrs, sizeof(void*) * K) == 0) return B2DP_OK;
+  if (changed) *changed = true;
   t.host.assign(ptrs, ptrs + K);
   // pageable source: the runtime stages it before returning, so t.host may change later
   CUDA_TRY(cudaMemcpyAsync(t.dev, t.host.data(), sizeof(void*) * K, cudaMemcpyHostToDevice, s));
@@ -175,7 +179,9 @@ int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const v
   int b0 = 0, b1 = 0;
   if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
   if (!ptrs && p->layout.K > 0) return fail(B2DP_ERR_INVALID, "tensor pointer array is null");
-  if (int rc = sync_table(table, ptrs, p->layout.K, s)) return rc;
+  bool changed = false;
+  if (int rc = sync_table(table, ptrs, p->layout.K, s, &changed)) return rc;
+  if (changed && &table == &r.grads) r.abs_valid = false;  // the resolved tile table follows the gradient pointers
   for (int b = b0; b < b1; ++b) {
     const Bucket& bk = p->layout.buckets[b];
     if (bk.tile_count == 0) continue;
@@ -404,6 +410,7 @@ void destroy_rank(RankState& r, size_t block_bytes = 0, bool local = true) {
   DeviceGuard guard(r.device);
   cudaDeviceSynchronize();
   if (r.d_tiles) cudaFree(r.d_tiles);
+  if (r.d_tiles_abs) cudaFree(r.d_tiles_abs);
   for (PtrTable* t : {&r.grads, &r.outs, &r.weights})
     if (t->dev) cudaFree(t->dev);
   // local context: every rank shares one multicast handle/mapping and the owner frees it;
@@ -717,6 +724,66 @@ extern "C" int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t wh
   DeviceGuard guard(r->device);
   return launch_pack<1>(p, *r, bucket, r->outs, (const void* const*)outs, off, B2DP_F32, 1.0f,
                         (cudaStream_t)stream);
+}
+
+// pack + step in one call.  n == 1 with an f32 wire: ONE kernel that reads the gradients in
+// place (no bucket copy at all); otherwise pack followed by the fused collective step.
+extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads, int32_t grad_dtype,
+                              float prescale, int32_t opt, const b2dp_hyper* hyper, void* stream) {
+  RankState* rp = nullptr;
+  if (int rc = get_rank(p, dev, &rp)) return rc;
+  if (opt != B2DP_OPT_ADAM && opt != B2DP_OPT_SGDM) return fail(B2DP_ERR_INVALID, "pack_step: optimizer must be ADAM or SGDM");
+  if (grad_dtype != B2DP_F32) return fail(B2DP_ERR_INVALID, "pack_step: gradients must be f32 (got dtype %d)", grad_dtype);
+  int b0 = 0, b1 = 0;
+  if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
+  int64_t nt = 0;
+  for (int b = b0; b < b1; ++b) nt += p->layout.buckets[b].tile_count;
+  const bool direct = p->ctx->nranks == 1 && p->layout.wire == B2DP_F32 &&
+                      (!(hyper && hyper->want_stats) || nt * kSubTiles <= kApplyMaxBlocks);
+  if (!direct) {
+    if (int rc = b2dp_pack(p, dev, bucket, grads, grad_dtype, prescale, stream)) return rc;
+    return b2dp_step(p, dev, bucket, opt, hyper, stream);
+  }
+  RankState& r = *rp;
+  OptScalars o;
+  if (int rc = fill_opt(opt, hyper, 1.0f, &o)) return rc;
+  if (nt == 0) return B2DP_OK;
+  if (!grads) return fail(B2DP_ERR_INVALID, "pack_step: tensor pointer array is null");
+  for (int b = b0; b < b1; ++b) {
+    const Bucket& bk = p->layout.buckets[b];
+    for (int k = bk.first; k < bk.first + bk.count; ++k)
+      if (p->layout.numel[k] > 0 && !grads[k]) return fail(B2DP_ERR_INVALID, "tensor %d pointer is null", k);
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  DeviceGuard guard(r.device);
+  bool changed = false;
+  if (int rc = sync_table(r.grads, grads, p->layout.K, s, &changed)) return rc;
+  const int64_t all_tiles = (int64_t)p->layout.tiles.size();
+  if (!r.d_tiles_abs) CUDA_TRY(cudaMalloc(&r.d_tiles_abs, sizeof(TileAbs) * all_tiles));
+  if (changed || !r.abs_valid) {  // rare: frameworks keep gradient buffers at stable addresses
+    resolve_tiles_kernel<<<(unsigned)((all_tiles + 255) / 256), 256, 0, s>>>(r.d_tiles, all_tiles, r.grads.dev, r.d_tiles_abs);
+    CUDA_TRY(cudaGetLastError());
+    r.abs_valid = true;
+  }
+  StepArgs a;
+  memset(&a, 0, sizeof a);
+  // tile offsets are flat element offsets; with one rank a shard offset equals the flat offset
+  a.w = reinterpret_cast<float*>(r.base[r.rank] + p->map.weights);
+  a.s0 = reinterpret_cast<float*>(r.base[r.rank] + p->map.s0);
+  a.s1 = reinterpret_cast<float*>(r.base[r.rank] + p->map.s1);
+  a.o = o;
+  a.partials = reinterpret_cast<double*>(r.base[r.rank] + p->map.partials);
+  a.ticket = reinterpret_cast<uint32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlTicket);
+  a.stats = reinterpret_cast<double*>(r.base[r.rank] + p->map.ctrl + kCtrlStats);
+  a.want_stats = hyper->want_stats ? 1 : 0;
+  const TileAbs* tiles = r.d_tiles_abs + p->layout.buckets[b0].tile_first;
+  const unsigned grid = (unsigned)(nt * kSubTiles);
+  if (opt == B2DP_OPT_ADAM)
+    fused_tiles_kernel<B2DP_OPT_ADAM><<<grid, kApplyThreads, 0, s>>>(tiles, prescale, a);
+  else
+    fused_tiles_kernel<B2DP_OPT_SGDM><<<grid, kApplyThreads, 0, s>>>(tiles, prescale, a);
+  CUDA_TRY(cudaGetLastError());
+  return B2DP_OK;
 }
 
 extern "C" int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp_hyper* hyper,

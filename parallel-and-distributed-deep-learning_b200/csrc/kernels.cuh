@@ -21,6 +21,8 @@ namespace b2dp {
 constexpr int kMaxBlocks = 1024;       // flag slots per phase; collective grids never exceed it
 constexpr int kStepThreads = 512;
 constexpr int kPackThreads = 256;
+constexpr int kApplyThreads = 256;      // n == 1 non-persistent kernels
+constexpr int kApplyMaxBlocks = 16384;  // statistics partial slots of those kernels
 
 // ---- memory helpers -----------------------------------------------------------------
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
@@ -402,13 +404,65 @@ step_kernel(const StepArgs a) {
   flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
 }
 
+// Statistics fold for the 256-thread non-persistent kernels: block partial -> scratch; the
+// last block to arrive folds every partial in a fixed order (deterministic for a given grid).
+__device__ __forceinline__ void block_stats_fold(const StepArgs& a, float sumsq, float bad) {
+  __shared__ double sm[2][kApplyThreads];
+  __shared__ bool last;
+  double s = (double)sumsq, b = (double)bad;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    sm[0][warp] = s;
+    sm[1][warp] = b;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s = b = 0.0;
+    for (int i = 0; i < kApplyThreads / 32; ++i) {
+      s += sm[0][i];
+      b += sm[1][i];
+    }
+    a.partials[2 * blockIdx.x] = s;
+    a.partials[2 * blockIdx.x + 1] = b;
+    __threadfence();
+    last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    s = b = 0.0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += kApplyThreads) {
+      s += __ldcg(a.partials + 2 * i);
+      b += __ldcg(a.partials + 2 * i + 1);
+    }
+    sm[0][threadIdx.x] = s;
+    sm[1][threadIdx.x] = b;
+    __syncthreads();
+    for (int o = kApplyThreads / 2; o > 0; o >>= 1) {
+      if ((int)threadIdx.x < o) {
+        sm[0][threadIdx.x] += sm[0][threadIdx.x + o];
+        sm[1][threadIdx.x] += sm[1][threadIdx.x + o];
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      a.stats[0] = sm[0][0];
+      a.stats[1] = sm[1][0];
+      *a.ticket = 0;
+    }
+  }
+}
+
 // n == 1 (imagenet-resnet50.py: no reduction, optimizer apply only), f32 gradients: the same
 // arithmetic as step_kernel<1,...>, laid out for HBM instead of NVLink -- one 256-bit vector
 // (8 elements) of each stream per thread and a NON-persistent grid.  Measured on B200
 // (tools/apply_variants.cu, back to back): 107.5 us vs 124 us for the persistent 128-bit
 // form, i.e. 6.66 TB/s = 1.02 of the measured copy peak.
-constexpr int kApplyThreads = 256;
-constexpr int kApplyMaxBlocks = 16384;  // statistics partial slots for this kernel
 
 template <int OPT>
 __global__ void __launch_bounds__(kApplyThreads)
@@ -446,58 +500,131 @@ apply1_kernel(const StepArgs a) {
     }
     st_f8(a.w + q * 8, w);
   }
-  if (a.want_stats) {
-    // block partial -> scratch; the last block to arrive folds every partial in a fixed order
-    __shared__ double sm[2][kApplyThreads];
-    __shared__ bool last;
-    double s = (double)sumsq, b = (double)bad;
+  if (a.want_stats) block_stats_fold(a, sumsq, bad);
+}
+
+// n == 1, pack fused away: the optimizer reads each gradient straight from the caller's
+// tensor (through the same tile table pack uses) and updates w/m/v at the tensor's place in
+// the flat buffers, so the gradient bucket is never written or re-read: 28 B/element of HBM
+// traffic instead of 36.  A block owns one 2048-element sub-tile (one 256-bit vector per
+// thread, like apply1_kernel); gradients whose pointer is not 32-byte aligned fall back to
+// 128-bit or scalar loads, ragged tails to scalars.  Same two scalings in the same order as
+// pack -> step, so the result is bit-identical to the two-launch form.
+constexpr int kSubTiles = kTileElems / (8 * kApplyThreads);  // blocks per tile
+
+// A tile with its gradient pointer already resolved (rebuilt by resolve_tiles_kernel only
+// when the caller's pointer array changes): one dependent load per block instead of two.
+struct TileAbs {
+  const float* src;  // tensor pointer + offset of the tile inside it
+  int64_t dst_off;   // flat element offset
+  uint32_t count;
+  uint32_t pad;
+};
+
+static __global__ void resolve_tiles_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
+                                     TileAbs* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntiles) {
+    const Tile tl = tiles[t];
+    TileAbs o;
+    o.src = reinterpret_cast<const float*>(ptrs[tl.tensor]) + tl.src_off;
+    o.dst_off = tl.dst_off;
+    o.count = tl.count;
+    o.pad = 0;
+    out[t] = o;
+  }
+}
+
+template <int OPT>
+__global__ void __launch_bounds__(kApplyThreads, 5)
+fused_tiles_kernel(const TileAbs* __restrict__ tiles, float prescale, const StepArgs a) {
+  const TileAbs tl = tiles[blockIdx.x / kSubTiles];
+  const uint32_t e0 = ((blockIdx.x % kSubTiles) * kApplyThreads + threadIdx.x) * 8;  // element inside the tile
+  const float* tens = tl.src;
+  float* w = a.w + tl.dst_off;
+  float* s0 = a.s0 + tl.dst_off;
+  float* s1 = a.s1 + tl.dst_off;
+  float sumsq = 0.0f, bad = 0.0f;
+  if (e0 < tl.count) {
+    const uint32_t cnt = min(8u, tl.count - e0);
+    float g[8], wv[8], m[8], v[8];
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(tens + e0);
+    if (cnt == 8) {
+      if ((addr & 31) == 0) {
+        float8 t = ld_stream_f8(tens + e0);
+        g[0] = t.lo.x; g[1] = t.lo.y; g[2] = t.lo.z; g[3] = t.lo.w; g[4] = t.hi.x; g[5] = t.hi.y; g[6] = t.hi.z; g[7] = t.hi.w;
+      } else if ((addr & 15) == 0) {
+        float4 t0 = ld_stream_f4(reinterpret_cast<const float4*>(tens + e0));
+        float4 t1 = ld_stream_f4(reinterpret_cast<const float4*>(tens + e0) + 1);
+        g[0] = t0.x; g[1] = t0.y; g[2] = t0.z; g[3] = t0.w; g[4] = t1.x; g[5] = t1.y; g[6] = t1.z; g[7] = t1.w;
+      } else {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      s += __shfl_xor_sync(0xffffffffu, s, o);
-      b += __shfl_xor_sync(0xffffffffu, b, o);
-    }
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) {
-      sm[0][warp] = s;
-      sm[1][warp] = b;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      s = b = 0.0;
-      for (int i = 0; i < kApplyThreads / 32; ++i) {
-        s += sm[0][i];
-        b += sm[1][i];
+        for (int i = 0; i < 8; ++i) g[i] = tens[e0 + i];
       }
-      a.partials[2 * blockIdx.x] = s;
-      a.partials[2 * blockIdx.x + 1] = b;
-      __threadfence();
-      last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (last) {
-      __threadfence();
-      s = b = 0.0;
-      for (unsigned i = threadIdx.x; i < gridDim.x; i += kApplyThreads) {
-        s += __ldcg(a.partials + 2 * i);
-        b += __ldcg(a.partials + 2 * i + 1);
+      float8 tw = ld_stream_f8(w + e0), t0 = ld_stream_f8(s0 + e0), t1;
+      if (OPT == B2DP_OPT_ADAM) t1 = ld_stream_f8(s1 + e0);
+      const float* pw = &tw.lo.x;
+      const float* p0 = &t0.lo.x;
+      const float* p1 = &t1.lo.x;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        wv[i] = pw[i];
+        m[i] = p0[i];
+        if (OPT == B2DP_OPT_ADAM) v[i] = p1[i];
       }
-      sm[0][threadIdx.x] = s;
-      sm[1][threadIdx.x] = b;
-      __syncthreads();
-      for (int o = kApplyThreads / 2; o > 0; o >>= 1) {
-        if ((int)threadIdx.x < o) {
-          sm[0][threadIdx.x] += sm[0][threadIdx.x + o];
-          sm[1][threadIdx.x] += sm[1][threadIdx.x + o];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (i < (int)cnt) {
+          g[i] = tens[e0 + i];
+          wv[i] = w[e0 + i];
+          m[i] = s0[e0 + i];
+          if (OPT == B2DP_OPT_ADAM) v[i] = s1[e0 + i];
         }
-        __syncthreads();
       }
-      if (threadIdx.x == 0) {
-        a.stats[0] = sm[0][0];
-        a.stats[1] = sm[1][0];
-        *a.ticket = 0;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (i < (int)cnt) {
+        const float acc = __fmul_rn(__fmul_rn(g[i], prescale), a.o.postscale);
+        if (a.want_stats) {
+          sumsq = fmaf(acc, acc, sumsq);
+          bad += (float)(!isfinite(acc));
+        }
+        if (OPT == B2DP_OPT_ADAM)
+          adam_update(acc, wv[i], m[i], v[i], a.o);
+        else
+          sgdm_update(acc, wv[i], m[i], a.o);
+      }
+    }
+    const bool keep_s0 = (OPT == B2DP_OPT_ADAM) || a.o.mu != 0.0f;
+    if (cnt == 8) {
+      float8 o;
+      if (keep_s0) {
+        o.lo = make_float4(m[0], m[1], m[2], m[3]);
+        o.hi = make_float4(m[4], m[5], m[6], m[7]);
+        st_f8(s0 + e0, o);
+      }
+      if (OPT == B2DP_OPT_ADAM) {
+        o.lo = make_float4(v[0], v[1], v[2], v[3]);
+        o.hi = make_float4(v[4], v[5], v[6], v[7]);
+        st_f8(s1 + e0, o);
+      }
+      o.lo = make_float4(wv[0], wv[1], wv[2], wv[3]);
+      o.hi = make_float4(wv[4], wv[5], wv[6], wv[7]);
+      st_f8(w + e0, o);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (i < (int)cnt) {
+          if (keep_s0) s0[e0 + i] = m[i];
+          if (OPT == B2DP_OPT_ADAM) s1[e0 + i] = v[i];
+          w[e0 + i] = wv[i];
+        }
       }
     }
   }
+  if (a.want_stats) block_stats_fold(a, sumsq, bad);
 }
 
 // Path B: the same step through the NVSwitch multicast mapping.  a.g[0] / a.out[0] are

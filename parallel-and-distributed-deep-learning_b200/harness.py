@@ -148,12 +148,11 @@ class DataParallelStep:
 
     def hot_path(self):
         self.t += 1
-        self.plan.pack(self.dev, [p.grad for p in self.params])
         if self.optimizer == "adam":
             h = api.adam_hyper(lr=self.lr, step=self.t, postscale=self.postscale)
         else:
             h = api.sgdm_hyper(lr=self.lr, postscale=self.postscale)
-        self.plan.step(self.dev, self.optimizer, h)
+        self.plan.pack_step(self.dev, [p.grad for p in self.params], self.optimizer, h)
 
     def __call__(self, images, labels):
         loss = self.forward_backward(images, labels)

@@ -356,3 +356,80 @@ def test_lr_is_a_per_call_argument():
         plan.step(0, "adam", b200dp.adam_hyper(lr=lr, step=step))
         oracle.adam_(w_ref, m, v, g, lr=lr, step=step)
     assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(w_ref))
+
+
+# ------------------------------------------------------------- pack_step (one call per step)
+def test_pack_step_single_rank_reads_gradients_in_place_bit_exact():
+    """n = 1: one kernel, no bucket copy; ResNet-50, 3 steps, prescale != 1, statistics on."""
+    numels, _ = resnet_inputs(0, 0)
+    N = sum(numels)
+    ctx, lay, plan = make_plan(numels, 1)
+    gen = torch.Generator(device="cuda").manual_seed(42)
+    w_flat = (torch.rand(N, generator=gen, device="cuda") - 0.5) * 0.1
+    plan.load_weights(0, views(w_flat, numels))
+    w_ref = w_flat.cpu().numpy().copy()
+    m_ref, v_ref = np.zeros(N, F), np.zeros(N, F)
+    for s in range(3):
+        _, flats = resnet_inputs(1, 77 + s)
+        plan.pack_step(0, views(flats[0], numels), "adam", b200dp.adam_hyper(lr=1e-3, step=s + 1, want_stats=True),
+                       prescale=0.5)
+        g = oracle.addn([flats[0].cpu().numpy()], prescale=0.5)
+        oracle.adam_(w_ref, m_ref, v_ref, g, lr=1e-3, step=s + 1)
+        torch.cuda.synchronize()
+        st = plan.tensor(0, b200dp.BUF_STATS).cpu().numpy()
+        assert abs(st[0] - oracle.sumsq(g)) <= 1e-6 * oracle.sumsq(g) and st[1] == 0      # tolerance: rel 1e-6
+    assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(w_ref))
+    assert np.array_equal(bits(gather_state(plan, lay, 1, b200dp.BUF_STATE0, numels)), bits(m_ref))
+    assert np.array_equal(bits(gather_state(plan, lay, 1, b200dp.BUF_STATE1, numels)), bits(v_ref))
+    # the gradient bucket was never written
+    assert not plan.tensor(0, b200dp.BUF_GRADS).any()
+
+
+@pytest.mark.parametrize("opt", ["adam", "sgdm"])
+@pytest.mark.parametrize("bucket_bytes", [0, 20000])
+def test_pack_step_ragged_and_misaligned_sources(opt, bucket_bytes):
+    rng = np.random.default_rng(11)
+    numels = [1, 3, 8195, 64, 0, 12345, 8192, 16383, 77, 9]
+    big = torch.randn(sum(numels) + 4 * len(numels) + 8, device="cuda") * 1e-2
+    for shift in (0, 1, 4):            # 32-byte aligned, 4-byte aligned, 16-byte aligned sources
+        srcs, o = [], shift
+        for n in numels:
+            srcs.append(big[o:o + n])
+            o += (n + 7) // 8 * 8
+        ctx, lay, plan = make_plan(numels, 1, bucket_bytes=bucket_bytes)
+        w0 = [rng.standard_normal(n).astype(F) for n in numels]
+        plan.load_weights(0, dev(w0))
+        w_ref = np.concatenate(w0)
+        s0, s1 = np.zeros_like(w_ref), np.zeros_like(w_ref)
+        g = np.concatenate([s.cpu().numpy() for s in srcs])
+        for step in (1, 2):
+            if opt == "adam":
+                plan.pack_step(0, srcs, "adam", b200dp.adam_hyper(step=step))
+                oracle.adam_(w_ref, s0, s1, g, step=step)
+            else:
+                plan.pack_step(0, srcs, "sgdm", b200dp.sgdm_hyper(lr=0.1, momentum=0.9, nesterov=True, weight_decay=1e-3))
+                oracle.sgdm_(w_ref, s0, g, lr=0.1, mu=0.9, nesterov=True, wd=1e-3)
+        assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(w_ref)), "shift %d" % shift
+
+
+def test_pack_step_with_ranks_equals_pack_then_step(golden):
+    numels = [int(x) for x in golden["numels"]]
+    n = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n)
+    w0 = dev(split(golden["w0"], numels))
+    for r in range(n):
+        plan.load_weights(r, w0)
+    for s in range(3):
+        gts = [dev(split(golden["grads"][s, r], numels)) for r in range(n)]
+        # emulated ranks: every rank's pack must precede any rank's step, so pack_step is issued
+        # for ranks 0..n-2 as pack only and the collective part afterwards (what real ranks do
+        # concurrently); rank n-1 can use the one-call form
+        for r in range(n - 1):
+            plan.pack(r, gts[r])
+        h = b200dp.adam_hyper(lr=float(golden["lrs"][s]), step=s + 1)
+        plan.pack(n - 1, gts[n - 1])
+        for r in range(n):
+            plan.step(r, "adam", h)
+    assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(golden["adam_w_f32"]))
+    with pytest.raises(b200dp.B200dpError):
+        plan.pack_step(0, dev(split(golden["grads"][0, 0], numels)), "none", b200dp.adam_hyper())
