@@ -459,8 +459,8 @@ def run_b200dp(args):
                     "traffic": load_traffic("fused_n1" if fused else "step_n1")}
     else:
         wire_b = 2 if args.wire == "bf16" else 4
-        if plan.path == "multicast":   # inbound: S/n reduced + (n-1)/n*S replicated stores; outbound the mirror image
-            nvl_bytes = float(S)
+        if plan.path == "multicast":   # inbound: S/n reduced + S replicated stores (the switch also writes the
+            nvl_bytes = S * (1.0 + 1.0 / n)   # sender's own copy); outbound the mirror image: S fetched + S/n stored
         else:                          # per GPU per direction: RS reads in + AG writes in
             nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S
         achieved = nvl_bytes / (step_avg_ms * 1e-3) / 1e9

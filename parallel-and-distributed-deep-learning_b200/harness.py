@@ -132,7 +132,15 @@ class DataParallelStep:
         torch.cuda.current_stream().synchronize()
         for k, p in enumerate(self.params):
             off = plan.layout.tensor_offset(k)
-            p.data = flat[off:off + p.numel()].view(p.shape)
+            seg = flat[off:off + p.numel()]
+            if p.dim() == 4 and not p.data.is_contiguous() and p.data.is_contiguous(memory_format=torch.channels_last):
+                # keep channels_last conv kernels channels_last (dense OHWI memory): cuDNN then needs
+                # no per-step layout copies; autograd gives the gradient the same strides
+                o, i, h, w = p.shape
+                p.data = seg.view(o, h, w, i).permute(0, 3, 1, 2)
+            else:
+                p.data = seg.view(p.shape)
+        self._checked_strides = False
         self.optimizer, self.lr, self.t = optimizer, lr, 0
         self.postscale = 1.0 / plan.ctx.nranks if mean_over_ranks else 1.0
 
@@ -148,6 +156,12 @@ class DataParallelStep:
 
     def hot_path(self):
         self.t += 1
+        if not self._checked_strides:   # flat position k of w and of g must be the same element
+            for p in self.params:
+                sig = lambda t: [st for st, sz in zip(t.stride(), t.shape) if sz > 1]   # size-1 dims carry no layout
+                if sig(p.grad) != sig(p):
+                    raise RuntimeError("gradient strides %s differ from parameter strides %s" % (p.grad.stride(), p.stride()))
+            self._checked_strides = True
         if self.optimizer == "adam":
             h = api.adam_hyper(lr=self.lr, step=self.t, postscale=self.postscale)
         else:
