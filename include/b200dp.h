@@ -231,6 +231,18 @@ int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t which, void* 
                 void* stream);
 int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* weights, void* stream);
 
+/* Step-0 and per-epoch helpers of the Horovod surface (collective calls, like step):
+ * broadcast -- the root rank's flat buffer (B2DP_BUF_WEIGHTS or B2DP_BUF_REDUCED) is stored
+ * into every rank's copy: hvd.callbacks.BroadcastGlobalVariablesCallback(0)
+ * (imagenet-resnet50-hvd.py:111).
+ * allreduce_small -- latency-bound one-shot all-reduce of count <= 1024 fp32 values in
+ * caller-owned device memory (out = rank-order sum * postscale): metric averaging,
+ * hvd.callbacks.MetricAverageCallback (imagenet-resnet50-hvd.py:113).  More than 1024 values
+ * returns B2DP_ERR_TOO_LARGE (use b2dp_allreduce). */
+int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t root, void* stream);
+int b2dp_allreduce_small(b2dp_plan* p, int32_t dev, const float* in, float* out, int32_t count,
+                         float postscale, void* stream);
+
 /* Scalar the Adam kernel multiplies by: lr*sqrt(1-beta2^t)/(1-beta1^t) in fp32, exposed
  * so a checker can use the library's exact value. */
 float b2dp_adam_alpha(float lr, float beta1, float beta2, int64_t step);

@@ -317,5 +317,17 @@ class Plan:
         check(self._L.b2dp_allreduce(self._h, dev, bucket, postscale,
                                      self._stream(stream, dev)))
 
+    def broadcast(self, dev, root=0, which=BUF_WEIGHTS, stream=None):
+        """Collective: the root rank's flat buffer overwrites every rank's copy."""
+        check(self._L.b2dp_broadcast(self._h, dev, which, int(root), self._stream(stream, dev)))
+
+    def allreduce_small(self, dev, src, dst, postscale=1.0, stream=None):
+        """Collective one-shot all-reduce of <= 1024 fp32 values (torch CUDA tensors src -> dst)."""
+        if src.numel() != dst.numel():
+            raise ValueError("allreduce_small: src and dst sizes differ")
+        vp = ctypes.c_void_p
+        check(self._L.b2dp_allreduce_small(self._h, dev, vp(src.data_ptr()), vp(dst.data_ptr()), src.numel(),
+                                           postscale, self._stream(stream, dev)))
+
     def check(self, dev, stream=None):
         check(self._L.b2dp_plan_check(self._h, dev, self._stream(stream, dev)))

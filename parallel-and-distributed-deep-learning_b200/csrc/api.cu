@@ -39,6 +39,7 @@ struct BlockMap {
   size_t flags = 0;      // 2 phases * kMaxBlocks * kMaxRanks u32
   size_t ctrl = 0;       // status word, ticket, stats
   size_t partials = 0;   // 2 doubles per block
+  size_t small = 0;      // small-message all-reduce slots: 2 halves x kMaxRanks x kSmallMax f32
   size_t grads = 0, weights = 0, reduced = 0, s0 = 0, s1 = 0, end = 0;
 };
 
@@ -54,6 +55,8 @@ BlockMap make_map(const b2dp_layout& l) {
   off += 4096;
   m.partials = off;
   off += align_up(size_t(2) * kApplyMaxBlocks * sizeof(double), 4096);
+  m.small = off;
+  off += align_up(size_t(2) * kMaxRanks * kSmallMax * sizeof(float), 4096);
   m.grads = off;
   off += align_up((size_t)l.total * wire, 4096);
   m.weights = off;
@@ -93,6 +96,10 @@ struct RankState {
   // Path B: the plan's multicast object as seen by this rank
   unsigned long long mc_handle = 0, mc_va = 0;
   bool mc_owner = false, mc_joined = false, mc_bound = false;
+  uint32_t small_calls = 0;          // parity selects the slot half
+  float* small_out = nullptr;        // emulated ranks: the sum phase is deferred to the last rank's call
+  int32_t small_count = 0;
+  float small_post = 1.0f;
 };
 
 }  // namespace
@@ -804,6 +811,104 @@ extern "C" int b2dp_all_gather(b2dp_plan* p, int32_t dev, int32_t bucket, void* 
 
 extern "C" int b2dp_allreduce(b2dp_plan* p, int32_t dev, int32_t bucket, float postscale, void* stream) {
   return run_collective(p, dev, bucket, B2DP_OPT_NONE, nullptr, postscale, 2, stream);
+}
+
+extern "C" int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t root, void* stream) {
+  RankState* rp = nullptr;
+  if (int rc = get_rank(p, dev, &rp)) return rc;
+  RankState& r = *rp;
+  const int n = p->ctx->nranks;
+  if (root < 0 || root >= n) return fail(B2DP_ERR_INVALID, "broadcast: root %d outside 0..%d", root, n - 1);
+  size_t off;
+  if (which == B2DP_BUF_WEIGHTS)
+    off = p->map.weights;
+  else if (which == B2DP_BUF_REDUCED)
+    off = p->map.reduced;
+  else
+    return fail(B2DP_ERR_INVALID, "broadcast: buffer %d is not WEIGHTS or REDUCED", which);
+  if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  if (n == 1 || p->layout.total == 0) return B2DP_OK;
+  DeviceGuard guard(r.device);
+  StepArgs a;
+  memset(&a, 0, sizeof a);
+  for (int i = 0; i < n; ++i) a.out[i] = reinterpret_cast<float*>(r.base[i] + off);
+  a.w = a.out[root];
+  a.nvec = p->layout.total / 4;
+  a.push = (r.rank == root) ? 1 : 0;
+  fill_comm(p, r, &a.c);
+  cudaStream_t s = (cudaStream_t)stream;
+  auto go = [&](auto kernel) {
+    const int grid = step_grid(kernel, r, a.nvec, 1, p->grid_cap);
+    kernel<<<grid, kStepThreads, 0, s>>>(a, root);
+    return cudaGetLastError();
+  };
+  cudaError_t e;
+  switch (n) {
+    case 2: e = go(broadcast_kernel<2>); break;
+    case 3: e = go(broadcast_kernel<3>); break;
+    case 4: e = go(broadcast_kernel<4>); break;
+    case 5: e = go(broadcast_kernel<5>); break;
+    case 6: e = go(broadcast_kernel<6>); break;
+    case 7: e = go(broadcast_kernel<7>); break;
+    default: e = go(broadcast_kernel<8>); break;
+  }
+  if (e != cudaSuccess) return fail(B2DP_ERR_CUDA, "broadcast launch: %s", cudaGetErrorString(e));
+  return B2DP_OK;
+}
+
+extern "C" int b2dp_allreduce_small(b2dp_plan* p, int32_t dev, const float* in, float* out, int32_t count,
+                                    float postscale, void* stream) {
+  RankState* rp = nullptr;
+  if (int rc = get_rank(p, dev, &rp)) return rc;
+  RankState& r = *rp;
+  if (count < 0 || count > kSmallMax)
+    return fail(count < 0 ? B2DP_ERR_INVALID : B2DP_ERR_TOO_LARGE, "allreduce_small: count %d outside 0..%d (use b2dp_allreduce for tensors)", count, kSmallMax);
+  if (count == 0) return B2DP_OK;
+  if (!in || !out) return fail(B2DP_ERR_INVALID, "allreduce_small: null pointer");
+  if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  const int n = p->ctx->nranks;
+  DeviceGuard guard(r.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  SmallArgs a;
+  memset(&a, 0, sizeof a);
+  for (int i = 0; i < n; ++i) a.slots[i] = reinterpret_cast<float*>(r.base[i] + p->map.small);
+  a.in = in;
+  a.out = out;
+  a.count = count;
+  a.half = (int)(r.small_calls++ & 1);
+  a.postscale = postscale;
+  fill_comm(p, r, &a.c);
+  if (!p->ctx->emulated) {
+    a.do_put = a.do_sum = 1;
+    small_allreduce_kernel<<<1, 256, 0, s>>>(a);
+    CUDA_TRY(cudaGetLastError());
+    return B2DP_OK;
+  }
+  // emulated ranks (one GPU, no waiting kernels): deposit now; after the last rank has
+  // deposited, run every rank's sum
+  a.do_put = 1;
+  a.do_sum = 0;
+  small_allreduce_kernel<<<1, 256, 0, s>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  r.small_out = out;
+  r.small_count = count;
+  r.small_post = postscale;
+  if (r.rank == n - 1) {
+    for (auto& q : p->rs) {
+      SmallArgs b = a;
+      b.do_put = 0;
+      b.do_sum = 1;
+      b.c.rank = q->rank;
+      b.out = q->small_out;
+      b.count = q->small_count;
+      b.postscale = q->small_post;
+      if (!b.out) return fail(B2DP_ERR_STATE, "allreduce_small: emulated rank %d never made its call", q->rank);
+      small_allreduce_kernel<<<1, 256, 0, s>>>(b);
+      CUDA_TRY(cudaGetLastError());
+      q->small_out = nullptr;
+    }
+  }
+  return B2DP_OK;
 }
 
 extern "C" float b2dp_adam_alpha(float lr, float beta1, float beta2, int64_t step) {

@@ -711,4 +711,58 @@ gather_kernel(const StepArgs a) {
   flag_barrier(a.c, 1);
 }
 
+// ---- step-0 / per-epoch helpers -----------------------------------
+// broadcast: the root stores its flat buffer into every rank's copy (what
+// hvd.BroadcastGlobalVariablesCallback(0) does once, imagenet-resnet50-hvd.py:111).
+// a.w = root's buffer as seen from this GPU; a.out[r] = rank r's buffer; a.push = 1 on the root.
+template <int N>
+__global__ void __launch_bounds__(kStepThreads)
+broadcast_kernel(const StepArgs a, int root) {
+  flag_barrier(a.c, 0);  // every rank is ready to be overwritten
+  if (a.push) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride) {
+      float4 v = ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q);
+#pragma unroll
+      for (int r = 0; r < N; ++r)
+        if (r != root) st_f4(reinterpret_cast<float4*>(a.out[r]) + q, v);
+    }
+  }
+  flag_barrier(a.c, 1);  // the data has landed everywhere
+}
+
+// Small-message all-reduce (metric averaging, hvd.MetricAverageCallback, -hvd.py:113): latency
+// bound, so one shot -- every rank deposits its <= 1024 values into its slot on every rank,
+// one flag barrier, every rank adds the n slots in rank order.  Slots are double-buffered by
+// call parity so a fast rank's next call cannot overwrite what a slow rank still reads.
+constexpr int kSmallMax = 1024;
+
+struct SmallArgs {
+  float* slots[kMaxRanks];  // [half][rank][kSmallMax] region of every rank
+  const float* in;
+  float* out;
+  int32_t count;
+  int32_t half;
+  float postscale;
+  int32_t do_put, do_sum;   // emulated ranks run the two phases as separate launches
+  Comm c;
+};
+
+static __global__ void __launch_bounds__(256) small_allreduce_kernel(const SmallArgs a) {
+  const size_t mine = ((size_t)a.half * kMaxRanks + a.c.rank) * kSmallMax;
+  if (a.do_put)
+    for (int i = threadIdx.x; i < a.count; i += blockDim.x) {
+      const float v = a.in[i];
+      for (int r = 0; r < a.c.n; ++r) a.slots[r][mine + i] = v;
+    }
+  flag_barrier(a.c, 0);
+  if (a.do_sum)
+    for (int i = threadIdx.x; i < a.count; i += blockDim.x) {
+      const float* base = a.slots[a.c.rank] + (size_t)a.half * kMaxRanks * kSmallMax + i;
+      float acc = __ldcg(base);
+      for (int r = 1; r < a.c.n; ++r) acc = __fadd_rn(acc, __ldcg(base + (size_t)r * kSmallMax));
+      a.out[i] = __fmul_rn(acc, a.postscale);
+    }
+}
+
 }  // namespace b2dp

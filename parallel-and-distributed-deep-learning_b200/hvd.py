@@ -116,7 +116,18 @@ def grouped_allreduce(tensors, average=None, op=None, prescale_factor=1.0, posts
 
 
 def allreduce(tensor, average=None, op=None, prescale_factor=1.0, postscale_factor=1.0, name=None):
-    """hvd.allreduce(tensor, average=None, op=None, prescale_factor=1.0, postscale_factor=1.0, name=None)"""
+    """hvd.allreduce(tensor, average=None, op=None, prescale_factor=1.0, postscale_factor=1.0, name=None).
+    Up to 1024 values (metric averaging, imagenet-resnet50-hvd.py:113) take the one-shot
+    latency-bound kernel; anything larger goes through the fused bucket path."""
+    _need_init()
+    if tensor.numel() <= 1024 and prescale_factor == 1.0 and str(tensor.dtype) == "torch.float32" and tensor.is_cuda:
+        import torch
+        _, post = _scales(average, op, prescale_factor, postscale_factor)
+        plan = _plan_for([256])     # any plan carries the small-message slots
+        src = tensor.contiguous()
+        out = torch.empty_like(src)
+        plan.allreduce_small(0, src, out, postscale=post)
+        return out
     return grouped_allreduce([tensor], average, op, prescale_factor, postscale_factor, name)[0]
 
 
@@ -185,6 +196,11 @@ class FusedDistributedAdam:
     def zero_grad(self, set_to_none=True):
         for p in self.params:
             p.grad = None
+
+    def broadcast_weights(self, root_rank=0):
+        """hvd.callbacks.BroadcastGlobalVariablesCallback(root_rank): every rank starts from the
+        root's weights (one kernel over the flat weight buffer)."""
+        self.plan.broadcast(0, root=root_rank)
 
     def step(self):
         self.t += 1

@@ -433,3 +433,50 @@ def test_pack_step_with_ranks_equals_pack_then_step(golden):
     assert np.array_equal(bits(read_tensors(plan, 0, numels)), bits(golden["adam_w_f32"]))
     with pytest.raises(b200dp.B200dpError):
         plan.pack_step(0, dev(split(golden["grads"][0, 0], numels)), "none", b200dp.adam_hyper())
+
+
+# ------------------------------------------------- step-0 / per-epoch helpers
+def test_broadcast_from_root_emulated_ranks():
+    numels = [5000, 64, 70001, 3]
+    n = 4
+    ctx, lay, plan = make_plan(numels, n)
+    rng = np.random.default_rng(21)
+    per_rank = [[rng.standard_normal(k).astype(F) for k in numels] for _ in range(n)]
+    for r in range(n):
+        plan.load_weights(r, dev(per_rank[r]))
+    for r in range(n):
+        plan.broadcast(r, root=2)
+    want = np.concatenate(per_rank[2])
+    for r in range(n):
+        assert np.array_equal(bits(read_tensors(plan, r, numels)), bits(want))
+    with pytest.raises(b200dp.B200dpError):
+        plan.broadcast(0, root=7)
+
+
+@pytest.mark.parametrize("count", [1, 7, 1024])
+def test_allreduce_small_matches_rank_order_sum(count):
+    n = 4
+    ctx, lay, plan = make_plan([256], n)
+    rng = np.random.default_rng(count)
+    for call in range(3):          # consecutive calls alternate the slot halves
+        vals = [(rng.standard_normal(count) * 10.0 ** rng.integers(-3, 3)).astype(F) for _ in range(n)]
+        ins = dev(vals)
+        outs = [torch.zeros(count, device="cuda") for _ in range(n)]
+        for r in range(n):
+            plan.allreduce_small(r, ins[r], outs[r], postscale=1.0 / n)
+        torch.cuda.synchronize()
+        ref = oracle.scale(oracle.addn(vals), 1.0 / n)
+        for r in range(n):
+            assert np.array_equal(bits(outs[r].cpu().numpy()), bits(ref)), "call %d rank %d" % (call, r)
+
+
+def test_allreduce_small_rejects_large_messages():
+    ctx, lay, plan = make_plan([256], 1)
+    x = torch.zeros(1025, device="cuda")
+    with pytest.raises(b200dp.B200dpError) as e:
+        plan.allreduce_small(0, x, x.clone())
+    assert e.value.code == b200dp._lib.ERR_TOO_LARGE
+    y = torch.arange(10, device="cuda", dtype=torch.float32)
+    out = torch.empty_like(y)
+    plan.allreduce_small(0, y, out, postscale=0.5)      # n = 1: value * postscale
+    assert torch.equal(out, y * 0.5)

@@ -130,6 +130,18 @@ def _rank_worker(rank, n, port, wire, q):
         got = plan.tensor(0, b200dp.BUF_WEIGHTS).cpu().numpy()
         flat_w = np.concatenate([got[lay.tensor_offset(k):lay.tensor_offset(k) + m] for k, m in enumerate(numels)])
         ok_w = bool(np.array_equal(bits(flat_w), bits(w_ref)))
+        # step-0 / per-epoch helpers: broadcast from the last rank, small all-reduce (Average)
+        plan.tensor(0, b200dp.BUF_WEIGHTS).fill_(float(rank))
+        torch.cuda.synchronize()
+        dist.barrier()
+        plan.broadcast(0, root=n - 1)
+        vals = [np.array([r + 0.25, -r, 1e-3 * r], F) for r in range(n)]
+        out = torch.zeros(3, device="cuda")
+        plan.allreduce_small(0, torch.from_numpy(vals[rank]).cuda(), out, postscale=1.0 / n)
+        torch.cuda.synchronize()
+        plan.check(0)
+        ok_w &= bool(torch.all(plan.tensor(0, b200dp.BUF_WEIGHTS) == float(n - 1)))
+        ok_w &= bool(np.array_equal(bits(out.cpu().numpy()), bits(oracle.scale(oracle.addn(vals), 1.0 / n))))
         dist.barrier()
         q.put((rank, ok_w, ok_ar, ok_nccl, ""))
     except Exception as e:  # report instead of hanging the parent
