@@ -240,6 +240,13 @@ int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* weights, voi
  * hvd.callbacks.MetricAverageCallback (imagenet-resnet50-hvd.py:113).  More than 1024 values
  * returns B2DP_ERR_TOO_LARGE (use b2dp_allreduce). */
 int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t root, void* stream);
+/* gather_state -- collective: every rank's shard of B2DP_BUF_STATE0 / STATE1 (Adam m / v, SGD
+ * accumulator) is assembled into B2DP_BUF_REDUCED of every rank in flat tensor order; follow
+ * with b2dp_unpack(B2DP_BUF_REDUCED) to get per-variable tensors.  What the checkpoint at the
+ * end of every script, model.save(...) (imagenet-resnet50-mirror.py:83-86), needs from an
+ * optimizer whose state is sharded across ranks.  Overwrites B2DP_BUF_REDUCED (for an f32
+ * wire that is the gradient bucket: call it between steps). */
+int b2dp_gather_state(b2dp_plan* p, int32_t dev, int32_t which, void* stream);
 int b2dp_allreduce_small(b2dp_plan* p, int32_t dev, const float* in, float* out, int32_t count,
                          float postscale, void* stream);
 

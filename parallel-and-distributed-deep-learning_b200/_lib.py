@@ -79,6 +79,7 @@ SIGNATURES = {
     "b2dp_unpack": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(_vp), _vp]),
     "b2dp_load_weights": (ctypes.c_int, [_vp, _i32, ctypes.POINTER(_vp), _vp]),
     "b2dp_broadcast": (ctypes.c_int, [_vp, _i32, _i32, _i32, _vp]),
+    "b2dp_gather_state": (ctypes.c_int, [_vp, _i32, _i32, _vp]),
     "b2dp_allreduce_small": (ctypes.c_int, [_vp, _i32, _vp, _vp, _i32, ctypes.c_float, _vp]),
     "b2dp_adam_alpha": (ctypes.c_float, [ctypes.c_float, ctypes.c_float, ctypes.c_float, _i64]),
     "b2dp_adam_apply_noalloc": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i64, ctypes.POINTER(Hyper), _vp, _vp]),

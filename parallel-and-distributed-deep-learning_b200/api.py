@@ -321,6 +321,19 @@ class Plan:
         """Collective: the root rank's flat buffer overwrites every rank's copy."""
         check(self._L.b2dp_broadcast(self._h, dev, which, int(root), self._stream(stream, dev)))
 
+    def gather_state(self, dev, which, stream=None):
+        """Collective: assemble the sharded optimizer state `which` (BUF_STATE0 / BUF_STATE1) into
+        BUF_REDUCED of every rank; unpack(which=BUF_REDUCED) then yields per-variable tensors."""
+        check(self._L.b2dp_gather_state(self._h, dev, which, self._stream(stream, dev)))
+
+    def state_tensors(self, dev, which, like):
+        """Convenience for single-caller use (n == 1 or a local context driving every rank in
+        order is the caller's job): gather + unpack into new tensors shaped like `like`."""
+        import torch
+        outs = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in like]
+        self.unpack(dev, outs, which=BUF_REDUCED)
+        return outs
+
     def allreduce_small(self, dev, src, dst, postscale=1.0, stream=None):
         """Collective one-shot all-reduce of <= 1024 fp32 values (torch CUDA tensors src -> dst)."""
         if src.numel() != dst.numel():

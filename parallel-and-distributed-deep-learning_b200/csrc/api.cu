@@ -813,6 +813,49 @@ extern "C" int b2dp_allreduce(b2dp_plan* p, int32_t dev, int32_t bucket, float p
   return run_collective(p, dev, bucket, B2DP_OPT_NONE, nullptr, postscale, 2, stream);
 }
 
+// Sharded optimizer state -> full flat buffer on every rank: each rank
+// pushes its shard of Adam m / v (or the SGD accumulator) into slice `rank` of every rank's
+// B2DP_BUF_REDUCED; b2dp_unpack(B2DP_BUF_REDUCED) then hands it out per variable, which is
+// what model.save() (imagenet-resnet50-mirror.py:83-86) needs from a sharded optimizer.
+extern "C" int b2dp_gather_state(b2dp_plan* p, int32_t dev, int32_t which, void* stream) {
+  RankState* rp = nullptr;
+  if (int rc = get_rank(p, dev, &rp)) return rc;
+  RankState& r = *rp;
+  size_t src_off;
+  if (which == B2DP_BUF_STATE0)
+    src_off = p->map.s0;
+  else if (which == B2DP_BUF_STATE1)
+    src_off = p->map.s1;
+  else
+    return fail(B2DP_ERR_INVALID, "gather_state: buffer %d is not STATE0 or STATE1", which);
+  if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  const int n = p->ctx->nranks;
+  DeviceGuard guard(r.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  for (const Bucket& bk : p->layout.buckets) {
+    if (bk.slice == 0) continue;
+    const size_t slice_elem0 = (size_t)bk.offset + (size_t)r.rank * bk.slice;
+    float* src = reinterpret_cast<float*>(r.base[r.rank] + src_off + (size_t)bk.shard_off * 4);
+    if (n == 1) {  // one rank: the shard is the whole bucket
+      CUDA_TRY(cudaMemcpyAsync(r.base[r.rank] + p->map.reduced + slice_elem0 * 4, src, (size_t)bk.slice * 4,
+                               cudaMemcpyDeviceToDevice, s));
+      continue;
+    }
+    StepArgs a;
+    memset(&a, 0, sizeof a);
+    for (int i = 0; i < n; ++i) a.out[i] = reinterpret_cast<float*>(r.base[i] + p->map.reduced + slice_elem0 * 4);
+    a.w = src;
+    a.nvec = bk.slice / 4;
+    a.push = 1;
+    fill_comm(p, r, &a.c);
+    a.c.rank = r.rank;
+    // gather_kernel skips r == rank, so the local copy is done explicitly
+    CUDA_TRY(cudaMemcpyAsync(a.out[r.rank], src, (size_t)bk.slice * 4, cudaMemcpyDeviceToDevice, s));
+    if (int rc = launch_gather(n, r, a, s)) return rc;
+  }
+  return B2DP_OK;
+}
+
 extern "C" int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t root, void* stream) {
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;

@@ -480,3 +480,32 @@ def test_allreduce_small_rejects_large_messages():
     out = torch.empty_like(y)
     plan.allreduce_small(0, y, out, postscale=0.5)      # n = 1: value * postscale
     assert torch.equal(out, y * 0.5)
+
+
+@pytest.mark.parametrize("n,bucket_bytes", [(1, 0), (4, 0), (4, 4096)])
+def test_gather_state_reassembles_sharded_adam_moments(golden, n, bucket_bytes):
+    """After training, m and v live sharded across ranks; gather_state + unpack returns them
+    per variable on every rank (what a checkpoint needs), equal to the oracle's."""
+    numels = [int(x) for x in golden["numels"]]
+    ng = golden["grads"].shape[1]
+    ctx, lay, plan = make_plan(numels, n, bucket_bytes=bucket_bytes)
+    w0 = dev(split(golden["w0"], numels))
+    for r in range(n):
+        plan.load_weights(r, w0)
+    w_ref = golden["w0"].copy()
+    m_ref, v_ref = np.zeros_like(w_ref), np.zeros_like(w_ref)
+    for s in range(2):
+        hg = [golden["grads"][s, r % ng] for r in range(n)]
+        for r in range(n):
+            plan.pack(r, dev(split(hg[r], numels)))
+        for r in range(n):
+            plan.step(r, "adam", b200dp.adam_hyper(step=s + 1))
+        oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(hg), step=s + 1)
+    for which, ref in ((b200dp.BUF_STATE0, m_ref), (b200dp.BUF_STATE1, v_ref)):
+        for r in range(n):
+            plan.gather_state(r, which)
+        for r in range(n):
+            got = read_tensors(plan, r, numels, b200dp.BUF_REDUCED)
+            assert np.array_equal(bits(got), bits(ref)), "rank %d" % r
+    with pytest.raises(b200dp.B200dpError):
+        plan.gather_state(0, b200dp.BUF_WEIGHTS)
