@@ -148,6 +148,76 @@ __global__ void __launch_bounds__(THREADS) apply_256_k(float* w, float* m, float
   }
 }
 
+// ---- TMA-staged variant: cp.async.bulk (1-D TMA) global->shared with an mbarrier, compute in
+// shared memory, cp.async.bulk shared->global.  One tile of each stream per CTA; several CTAs
+// per SM overlap load / compute / store.  Built to answer "would TMA/shared-memory staging
+// beat plain 256-bit loads for this 7-stream pass?" with a measurement.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+}
+template <int TILE, int MATH>
+__global__ void __launch_bounds__(256) apply_tma_k(float* w, float* m, float* v, const float* g, long n, P o) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* sg = reinterpret_cast<float*>(smem_raw);
+  float* sw = sg + TILE;
+  float* sm = sw + TILE;
+  float* sv = sm + TILE;
+  __shared__ __align__(8) unsigned long long bar;
+  const long e0 = (long)blockIdx.x * TILE;
+  if (e0 >= n) return;
+  const unsigned bytes = TILE * 4;
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(4 * bytes) : "memory");
+    bulk_g2s(sg, g + e0, bytes, &bar);
+    bulk_g2s(sw, w + e0, bytes, &bar);
+    bulk_g2s(sm, m + e0, bytes, &bar);
+    bulk_g2s(sv, v + e0, bytes, &bar);
+  }
+  {
+    unsigned done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done)
+                   : "r"(smem_u32(&bar))
+                   : "memory");
+  }
+#pragma unroll
+  for (int j = 0; j < TILE / (4 * 256); ++j) {
+    const int q = j * 256 + threadIdx.x;
+    float4 gg = reinterpret_cast<float4*>(sg)[q], ww = reinterpret_cast<float4*>(sw)[q];
+    float4 mm = reinterpret_cast<float4*>(sm)[q], vv = reinterpret_cast<float4*>(sv)[q];
+    if (MATH) {
+      adam1(gg.x, ww.x, mm.x, vv.x, o); adam1(gg.y, ww.y, mm.y, vv.y, o);
+      adam1(gg.z, ww.z, mm.z, vv.z, o); adam1(gg.w, ww.w, mm.w, vv.w, o);
+    } else {
+      mm.x += gg.x; vv.x += gg.x; ww.x += gg.x;
+    }
+    reinterpret_cast<float4*>(sw)[q] = ww;
+    reinterpret_cast<float4*>(sm)[q] = mm;
+    reinterpret_cast<float4*>(sv)[q] = vv;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bulk_s2g(m + e0, sm, bytes);
+    bulk_s2g(v + e0, sv, bytes);
+    bulk_s2g(w + e0, sw, bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+}
+
 __global__ void copy_k(const float4* a, float4* b, long nvec) {
   const long stride = (long)gridDim.x * blockDim.x;
   for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) st4(b + q, ld4<0>(a + q));
@@ -206,6 +276,21 @@ int main() {
   bench("adam  256-bit 256thr grid 4/SM", [&] { apply_256_k<256, 1><<<sms * 4, 256>>>(w, m, v, g, N / 8, o); }, B);
   bench("adam  256-bit 512thr grid 2/SM", [&] { apply_256_k<512, 1><<<sms * 2, 512>>>(w, m, v, g, N / 8, o); }, B);
   bench("adam  256-bit 256thr non-persistent", [&] { apply_256_k<256, 1><<<(int)((N / 8 + 255) / 256), 256>>>(w, m, v, g, N / 8, o); }, B);
+  {
+    auto k2 = apply_tma_k<2048, 1>;
+    auto k4 = apply_tma_k<4096, 1>;
+    auto k8 = apply_tma_k<8192, 1>;
+    auto k4s = apply_tma_k<4096, 0>;
+    CK(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 2048 * 4));
+    CK(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 4096 * 4));
+    CK(cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 8192 * 4));
+    CK(cudaFuncSetAttribute(k4s, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 4096 * 4));
+    bench("adam  TMA bulk tile 2048 (32 KB smem/CTA)", [&] { k2<<<(int)(N / 2048), 256, 4 * 2048 * 4>>>(w, m, v, g, N, o); }, B);
+    bench("adam  TMA bulk tile 4096 (64 KB smem/CTA)", [&] { k4<<<(int)(N / 4096), 256, 4 * 4096 * 4>>>(w, m, v, g, N, o); }, B);
+    bench("adam  TMA bulk tile 8192 (128 KB smem/CTA)", [&] { k8<<<(int)(N / 8192), 256, 4 * 8192 * 4>>>(w, m, v, g, N, o); }, B);
+    bench("strm  TMA bulk tile 4096 (no math)", [&] { k4s<<<(int)(N / 4096), 256, 4 * 4096 * 4>>>(w, m, v, g, N, o); }, B);
+    CK(cudaDeviceSynchronize());
+  }
   bench("strm  256-bit 256thr grid 4/SM (no math)", [&] { apply_256_k<256, 0><<<sms * 4, 256>>>(w, m, v, g, N / 8, o); }, B);
   return 0;
 }
