@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
     ap.add_argument("--path", default="auto", choices=["auto", "peer", "multicast"],
                     help="N>1 collective path: peer loads with rank-order sum (bit-exact) or NVSwitch multicast")
+    ap.add_argument("--overlap", action="store_true",
+                    help="issue each bucket's pack+step from autograd hooks while backward still runs (SURVEY 8f-1)")
+    ap.add_argument("--bucket-mb", type=float, default=0.0, help="bucket size in MB (0 = one bucket, the reference default)")
     ap.add_argument("--hotpath-only", action="store_true", help="time only pack+step on synthetic gradients")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-batch", type=int, default=32, help="CPU arm: images per step (configs[0])")
@@ -207,6 +210,7 @@ def workload_config(args, n, cpu=False):
         "global_batch": (args.ref_batch if cpu else args.batch * n), "per_gpu_batch": args.ref_batch if cpu else args.batch,
         "optimizer": args.optimizer, "wire_dtype": args.wire, "parallelism": "dp%d" % n,
         "collective_path": getattr(args, "path_used", "n/a"),
+        "buckets": getattr(args, "num_buckets", 1), "overlap_with_backward": bool(args.overlap),
         "conv_graph": "torch-CPU stand-in" if cpu else "torch+cuDNN stand-in (TF32 convs, as TF defaults)",
         "l2": "inputs_exceed_l2 (activations and 409 MB of w/m/v/g per step >> 126 MB L2)",
     }
@@ -237,7 +241,8 @@ def run_b200dp(args):
 
     numels = b200dp.resnet50_numels()
     ctx = b200dp.Context.rank(rank, n, local_rank)
-    lay = b200dp.Layout(numels, nranks=n, wire=args.wire)
+    bucket_bytes = int(args.bucket_mb * (1 << 20)) or (25 << 20 if args.overlap else 0)
+    lay = b200dp.Layout(numels, nranks=n, wire=args.wire, bucket_bytes=bucket_bytes)
     plan = b200dp.Plan(ctx, lay)
     if n > 1:
         session = "bench-%s-%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
@@ -257,6 +262,7 @@ def run_b200dp(args):
         dist.barrier()
 
     args.path_used = plan.path if n > 1 else "n/a (single GPU)"
+    args.num_buckets = lay.num_buckets
     B = args.batch
     gen = torch.Generator(device=device).manual_seed(7 + rank)
     host_gen = torch.Generator().manual_seed(7 + rank)
@@ -286,7 +292,7 @@ def run_b200dp(args):
         stepper = None
     else:
         model = harness.KerasResNet50().to(device).to(memory_format=torch.channels_last).train()
-        stepper = harness.DataParallelStep(model, plan, dev=0, optimizer=args.optimizer, lr=1e-3)
+        stepper = harness.DataParallelStep(model, plan, dev=0, optimizer=args.optimizer, lr=1e-3, overlap=args.overlap)
         x_dev = (torch.rand(B, 3, 224, 224, generator=gen, device=device) * 255.0).contiguous(
             memory_format=torch.channels_last)
         y_dev = torch.randint(0, 1000, (B,), generator=gen, device=device)
@@ -490,7 +496,7 @@ def run_b200dp(args):
         "value": n * B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
-        "clocks": clocks, "gpu_launches": launches_per_step * args.steps,
+        "clocks": clocks, "gpu_launches": launches_per_step * args.steps * lay.num_buckets,
         "gpu_launches_note": "libb200dp.so kernels per step: fused_tiles_kernel at n=1, pack_kernel + step kernel at n>1; "
                              "conv graph launches are torch/cuDNN's",
         "roofline": roofline, "hot_path": hot_path,

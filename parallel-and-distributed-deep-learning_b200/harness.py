@@ -121,9 +121,10 @@ class DataParallelStep:
     The model's parameters are made views of the plan's flat weight buffer, so the
     all-gathered weights are what the next forward reads (no unpack pass)."""
 
-    def __init__(self, model, plan, dev=0, optimizer="adam", lr=1e-3, mean_over_ranks=False):
+    def __init__(self, model, plan, dev=0, optimizer="adam", lr=1e-3, mean_over_ranks=False, overlap=False,
+                 params=None):
         self.model, self.plan, self.dev = model, plan, dev
-        self.params = model.keras_order_params()
+        self.params = list(params) if params is not None else model.keras_order_params()
         numels = [p.numel() for p in self.params]
         if numels != plan.layout.numels:
             raise ValueError("model parameters do not match the plan's tensor list")
@@ -143,6 +144,47 @@ class DataParallelStep:
         self._checked_strides = False
         self.optimizer, self.lr, self.t = optimizer, lr, 0
         self.postscale = 1.0 / plan.ctx.nranks if mean_over_ranks else 1.0
+        self.overlap = bool(overlap)
+        if self.overlap:
+            self._init_overlap()
+
+    # -- bucket pipeline overlapped with backward -----------------------
+    # Gradients appear in reverse layer order during backward.  As soon as the last gradient
+    # of a bucket exists, that bucket's pack + fused step is issued on a side stream, so the
+    # reduction of the late layers runs under the convolutions of the early ones (what Horovod's
+    # background fusion cycle does for hvd.DistributedOptimizer, imagenet-resnet50-hvd.py:101).
+    # Every rank walks the same autograd graph, so buckets complete -- and the collective calls
+    # are issued -- in the same order everywhere.
+    def _init_overlap(self):
+        lay = self.plan.layout
+        self._bucket_of = [lay.tensor_bucket(k) for k in range(len(self.params))]
+        self._bucket_size = [0] * lay.num_buckets
+        for b in self._bucket_of:
+            self._bucket_size[b] += 1
+        self._left = list(self._bucket_size)
+        self._side = torch.cuda.Stream(device=self.plan.ctx.devices[self.dev])
+        self._hyper = None
+        for k, p in enumerate(self.params):
+            p.register_post_accumulate_grad_hook(lambda _p, k=k: self._on_grad(k))
+
+    def _on_grad(self, k):
+        b = self._bucket_of[k]
+        self._left[b] -= 1
+        if self._left[b] == 0:
+            self._issue_bucket(b)
+
+    def _issue_bucket(self, b):
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)                 # every gradient of the bucket is enqueued before this point
+        self._side.wait_event(ready)
+        ptrs = [0 if p.grad is None else p.grad.data_ptr() for p in self.params]
+        self.plan.pack_step(self.dev, api.ptr_array(ptrs), self.optimizer, self._hyper, bucket=b, stream=self._side)
+
+    def _make_hyper(self):
+        if self.optimizer == "adam":
+            return api.adam_hyper(lr=self.lr, step=self.t, postscale=self.postscale)
+        return api.sgdm_hyper(lr=self.lr, postscale=self.postscale)
 
     def forward_backward(self, images, labels):
         for p in self.params:
@@ -169,8 +211,17 @@ class DataParallelStep:
         self.plan.pack_step(self.dev, [p.grad for p in self.params], self.optimizer, h)
 
     def __call__(self, images, labels):
-        loss = self.forward_backward(images, labels)
-        self.hot_path()
+        if not self.overlap:
+            loss = self.forward_backward(images, labels)
+            self.hot_path()
+            return loss
+        self.t += 1
+        self._hyper = self._make_hyper()
+        self._left = list(self._bucket_size)
+        loss = self.forward_backward(images, labels)     # the hooks issue each bucket as it completes
+        if any(self._left):
+            raise RuntimeError("backward produced no gradient for some tensors of a bucket")
+        torch.cuda.current_stream().wait_stream(self._side)   # the next forward reads the updated weights
         return loss
 
 

@@ -393,3 +393,70 @@ def test_hvd_module_one_process_per_gpu():
         assert not err, err
         assert ok_avg, "rank %d: hvd Average differs from the oracle" % rank
         assert ok_adam, "rank %d: fused Adam differs from the oracle" % rank
+
+
+# ------------------------------------------------------------------ 8f-1: bucket overlap, n ranks
+def _overlap_worker(rank, n, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=n, device_id=torch.device("cuda", rank))
+    try:
+        from b200dp import harness
+        from test_gpu_glue import _TinyNet
+        torch.backends.cuda.matmul.allow_tf32 = False
+        results = []
+        for tag, overlap, bucket_bytes in (("serial", False, 0), ("overlap", True, 600_000)):
+            torch.manual_seed(0)                      # same initial weights on every rank
+            model = _TinyNet().cuda()
+            numels = [p.numel() for p in model.keras_order_params()]
+            ctx = b200dp.Context.rank(rank, n, rank)
+            ctx.set_timeout(5.0)
+            lay = b200dp.Layout(numels, nranks=n, bucket_bytes=bucket_bytes)
+            plan = b200dp.Plan(ctx, lay)
+            plan.exchange("ov-%d-%s" % (port, tag))
+            dist.barrier()
+            stepper = harness.DataParallelStep(model, plan, overlap=overlap)
+            g = torch.Generator(device="cuda").manual_seed(100 + rank)     # different data per rank
+            for _ in range(3):
+                x = torch.randn(64, 256, generator=g, device="cuda")
+                y = torch.randint(0, 10, (64,), generator=g, device="cuda")
+                stepper(x, y)
+            torch.cuda.synchronize()
+            plan.check(0)
+            results.append(torch.cat([p.detach().flatten() for p in model.keras_order_params()]).clone())
+            dist.barrier()
+        same_as_serial = bool(torch.equal(results[0].view(torch.int32), results[1].view(torch.int32)))
+        gathered = [torch.empty_like(results[1]) for _ in range(n)]
+        dist.all_gather(gathered, results[1])
+        same_on_all = all(bool(torch.equal(gathered[0], t)) for t in gathered)
+        q.put((rank, same_as_serial, same_on_all, ""))
+    except Exception:
+        import traceback
+        q.put((rank, False, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+def test_bucket_overlap_with_backward_rank_contexts():
+    import torch.multiprocessing as mp
+    n = min(NGPU, 8)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_overlap_worker, args=(r, n, port, q)) for r in range(n)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(n)]
+    for p in procs:
+        p.join(60)
+    for rank, same_as_serial, same_on_all, err in sorted(results):
+        assert not err, err
+        assert same_as_serial, "rank %d: overlapped bucket pipeline differs from the serial step" % rank
+        assert same_on_all, "ranks ended with different weights"
