@@ -509,3 +509,41 @@ def test_gather_state_reassembles_sharded_adam_moments(golden, n, bucket_bytes):
             assert np.array_equal(bits(got), bits(ref)), "rank %d" % r
     with pytest.raises(b200dp.B200dpError):
         plan.gather_state(0, b200dp.BUF_WEIGHTS)
+
+
+def test_large_plan_offsets_beyond_32_bits():
+    """Maximum-size case: one 2^29+12,345-element tensor (2.1 GB per buffer), so byte offsets
+    pass 2^31; three 1M-element windows (start, middle, ragged end) are checked against the
+    oracle, bit-exact, through both the in-place fused kernel and pack -> step."""
+    n_el = (1 << 29) + 12345
+    numels = [4096, n_el, 777]
+    free, _ = torch.cuda.mem_get_info()
+    if free < 16 * (1 << 30):
+        pytest.skip("needs ~12 GB of free device memory")
+    ctx, lay, plan = make_plan(numels, 1)
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    g = [torch.randn(k, generator=gen, device="cuda") * 1e-2 for k in numels]
+    w = [torch.rand(k, generator=gen, device="cuda") - 0.5 for k in numels]
+    plan.load_weights(0, w)
+    plan.pack_step(0, g, "adam", b200dp.adam_hyper(step=1))          # fused in-place kernel
+    plan.pack(0, g)
+    plan.step(0, "adam", b200dp.adam_hyper(step=2))                  # pack -> apply1 kernel
+    torch.cuda.synchronize()
+    flat_w = plan.tensor(0, b200dp.BUF_WEIGHTS)
+    off = lay.tensor_offset(1)
+    for lo in (0, n_el // 2 + 3, n_el - 1_000_000):
+        hi = min(n_el, lo + 1_000_000)
+        ws = w[1][lo:hi].cpu().numpy().copy()
+        gs = g[1][lo:hi].cpu().numpy()
+        ms, vs = np.zeros_like(ws), np.zeros_like(ws)
+        oracle.adam_(ws, ms, vs, gs, step=1)
+        oracle.adam_(ws, ms, vs, gs, step=2)
+        got = flat_w[off + lo:off + hi].cpu().numpy()
+        assert np.array_equal(bits(got), bits(ws)), "window at %d" % lo
+    # the small tensor after the big one sits past 2^31 bytes too
+    off2 = lay.tensor_offset(2)
+    ws = w[2].cpu().numpy().copy()
+    ms, vs = np.zeros_like(ws), np.zeros_like(ws)
+    oracle.adam_(ws, ms, vs, g[2].cpu().numpy(), step=1)
+    oracle.adam_(ws, ms, vs, g[2].cpu().numpy(), step=2)
+    assert np.array_equal(bits(flat_w[off2:off2 + 777].cpu().numpy()), bits(ws))

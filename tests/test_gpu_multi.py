@@ -460,3 +460,24 @@ def test_bucket_overlap_with_backward_rank_contexts():
         assert not err, err
         assert same_as_serial, "rank %d: overlapped bucket pipeline differs from the serial step" % rank
         assert same_on_all, "ranks ended with different weights"
+
+
+# ------------------------------------------------------------------ failure detection
+@needs2
+def test_missing_peer_times_out_instead_of_hanging():
+    """If a rank never reaches a collective, the waiting kernel gives up after the context's
+    timeout and b2dp_plan_check reports B2DP_ERR_TIMEOUT -- the GPU is never left spinning."""
+    import time
+    ctx = b200dp.Context.local([0, 1])
+    ctx.set_timeout(0.5)
+    lay = b200dp.Layout([4096], nranks=2)
+    plan = b200dp.Plan(ctx, lay)
+    with torch.cuda.device(0):
+        plan.pack(0, [torch.ones(4096, device="cuda:0")])
+        t0 = time.time()
+        plan.step(0, "adam", b200dp.adam_hyper(step=1))      # rank 1 never calls step
+        with pytest.raises(b200dp.B200dpError) as e:
+            plan.check(0)
+        assert e.value.code == b200dp._lib.ERR_TIMEOUT
+        assert time.time() - t0 < 20
+        plan.check(0)                                        # the status word was cleared
