@@ -392,8 +392,15 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
       CUDA_TRY(cudaGetLastError());
       continue;
     }
-    const bool use_mc = p->path == B2DP_PATH_MULTICAST && a.c.use_flags && (mode == 0 || mode == 2);
-    if (use_mc) {
+    const bool use_mc = p->path == B2DP_PATH_MULTICAST && a.c.use_flags;
+    if (use_mc && mode == 3) {
+      char* mc = reinterpret_cast<char*>(r.mc_va);
+      a.out[0] = reinterpret_cast<float*>(mc + out_off + slice_elem0 * 4);
+      const int grid = step_grid(gather_mc_kernel, r, a.nvec, 1, p->mc_grid_cap);
+      gather_mc_kernel<<<grid, kStepThreads, 0, s>>>(a);
+      CUDA_TRY(cudaGetLastError());
+      rc = B2DP_OK;
+    } else if (use_mc) {
       char* mc = reinterpret_cast<char*>(r.mc_va);
       a.g[0] = mc + p->map.grads + slice_elem0 * wire;
       a.out[0] = reinterpret_cast<float*>(mc + out_off + slice_elem0 * 4);

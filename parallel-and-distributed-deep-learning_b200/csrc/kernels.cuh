@@ -686,7 +686,10 @@ step_mc_kernel(const StepArgs a) {
         } else {
           res = acc;
         }
-        multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + q, res);
+        if (a.push)
+          multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + q, res);
+        else
+          st_f4(reinterpret_cast<float4*>(a.w) + q, res);   // reduce-scatter + apply only (PS push)
       }
     }
   }
@@ -708,6 +711,18 @@ gather_kernel(const StepArgs a) {
     for (int r = 0; r < N; ++r)
       if (r != a.c.rank) st_f4(reinterpret_cast<float4*>(a.out[r]) + q, v);
   }
+  flag_barrier(a.c, 1);
+}
+
+// all-gather alone through the multicast mapping (PS pull on Path B): a.w = my slice
+// (unicast), a.out[0] = the same slice's multicast address.
+static __global__ void __launch_bounds__(kStepThreads)
+gather_mc_kernel(const StepArgs a) {
+  flag_barrier(a.c, 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride)
+    multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + q, ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q));
+  __threadfence_system();
   flag_barrier(a.c, 1);
 }
 

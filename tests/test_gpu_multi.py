@@ -224,6 +224,17 @@ def _path_b_checks(plan, lay, n, numels, local_devs, ops, sync):
     for dev in local_devs:
         got = _flat(plan, lay, numels, b200dp.BUF_WEIGHTS, dev)
         assert np.all(np.abs(got.astype(np.float64) - w_ref) <= lr * bound + 2 * np.spacing(np.abs(w_ref).astype(F)))
+    # (2b) the two-launch form (PS push / pull) through the multicast mapping: same bound
+    for dev in local_devs:
+        plan.tensor(dev, b200dp.BUF_STATE0).zero_()
+    sync()
+    ops.load(w0)
+    ops.put(hg)
+    ops.two_launch("sgdm", b200dp.sgdm_hyper(lr=lr, momentum=0.9))
+    sync()
+    for dev in local_devs:
+        got = _flat(plan, lay, numels, b200dp.BUF_WEIGHTS, dev)
+        assert np.all(np.abs(got.astype(np.float64) - w_ref) <= lr * bound + 2 * np.spacing(np.abs(w_ref).astype(F)))
     # (3) fused Adam, two steps, same-sign gradients: |dw| <= 3e-8
     for dev in local_devs:   # the SGD step above left its accumulator in the state shard
         plan.tensor(dev, b200dp.BUF_STATE0).zero_()
@@ -266,6 +277,7 @@ def test_path_b_multicast_local_context():
     ops.allreduce = lambda: each(lambda r: plan.allreduce(r))
     ops.load = lambda w: each(lambda r: plan.load_weights(r, views(torch.from_numpy(w).cuda(r), numels)))
     ops.step = lambda opt, h: each(lambda r: plan.step(r, opt, h))
+    ops.two_launch = lambda opt, h: (each(lambda r: plan.reduce_scatter_apply(r, opt, h)), each(lambda r: plan.all_gather(r)))
 
     def sync():
         for r in range(n):
@@ -296,6 +308,7 @@ def _rank_worker_mc(rank, n, port, q):
         ops.allreduce = lambda: plan.allreduce(0)
         ops.load = lambda w: plan.load_weights(0, views(torch.from_numpy(w).cuda(), numels))
         ops.step = lambda opt, h: plan.step(0, opt, h)
+        ops.two_launch = lambda opt, h: (plan.reduce_scatter_apply(0, opt, h), plan.all_gather(0))
         _path_b_checks(plan, lay, n, numels, [0], ops, torch.cuda.synchronize)
         plan.check(0)
         dist.barrier()

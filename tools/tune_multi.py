@@ -76,8 +76,17 @@ def main():
         def allreduce(r):
             plan.allreduce(r, postscale=1.0 / n)
 
-        configs = [("multicast", dict(mc_unroll=u, mc_grid_cap=c)) for u, c in itertools.product((1, 2, 4), (37, 74, 148, 296))]
-        configs += [("peer", dict(peer_unroll=u, grid_cap=c)) for u, c in itertools.product((1, 2), (74, 148, 296, 592))]
+        def rs_only(r):
+            plan.reduce_scatter_apply(r, "adam", b200dp.adam_hyper(step=t[0] + 1))
+
+        def ag_only(r):
+            plan.all_gather(r)
+
+        if os.environ.get("TUNE_FULL"):
+            configs = [("multicast", dict(mc_unroll=u, mc_grid_cap=c)) for u, c in itertools.product((1, 2, 4), (37, 74, 148, 296))]
+            configs += [("peer", dict(peer_unroll=u, grid_cap=c)) for u, c in itertools.product((1, 2), (74, 148, 296, 592))]
+        else:   # the chosen geometry only, plus the two halves of the step on their own
+            configs = [("multicast", dict(mc_unroll=1, mc_grid_cap=c)) for c in (74, 148)] + [("peer", dict(peer_unroll=0, grid_cap=296))]
         for path, knobs in configs:
             plan.set_path(path)
             plan.set_tuning(**knobs)
@@ -86,7 +95,10 @@ def main():
             for r in range(n):
                 with torch.cuda.device(r):
                     plan.check(r)
+            us_rs = time_all(n, rs_only)
+            us_ag = time_all(n, ag_only)
             row = {"n": n, "path": path, **knobs, "step_us": round(us_step, 1), "allreduce_us": round(us_ar, 1),
+                   "reduce_scatter_apply_us": round(us_rs, 1), "all_gather_us": round(us_ag, 1),
                    "step_busbw": round(S / us_step * 2 * (n - 1) / n / 1e3, 1)}
             results.append(row)
             print(json.dumps(row), flush=True)
