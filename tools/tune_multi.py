@@ -103,6 +103,48 @@ def main():
             results.append(row)
             print(json.dumps(row), flush=True)
         del plan, ctx
+    # Can the two directions overlap better than the fused kernel manages?  Run the two halves
+    # CONCURRENTLY (two plans, so each has its own flag words; two streams per device).
+    if os.environ.get("TUNE_CONCURRENT", "1") == "1":
+        for n in [x for x in (8,) if x <= ndev]:
+            ctx = b200dp.Context.local(list(range(n)))
+            ctx.set_timeout(5.0)
+            lay = b200dp.Layout(numels, nranks=n)
+            plans = [b200dp.Plan(ctx, lay), b200dp.Plan(ctx, lay)]
+            for pl in plans:
+                pl.enable_multicast()
+            s1 = [torch.cuda.Stream(device=r) for r in range(n)]
+            s2 = [torch.cuda.Stream(device=r) for r in range(n)]
+            for r in range(n):
+                with torch.cuda.device(r):
+                    g = torch.randn(sum(numels), device="cuda:%d" % r) * 1e-3
+                    for pl in plans:
+                        pl.pack(r, views(g, numels))
+                        pl.tensor(r, b200dp.BUF_WEIGHTS).uniform_(-0.05, 0.05)
+            for path, knobs in (("multicast", dict(mc_unroll=1, mc_grid_cap=74)), ("multicast", dict(mc_unroll=1, mc_grid_cap=37)),
+                                ("peer", dict(peer_unroll=0, grid_cap=148)), ("peer", dict(peer_unroll=0, grid_cap=296))):
+                for pl in plans:
+                    pl.set_path(path)
+                    pl.set_tuning(**knobs)
+
+                def both(r):
+                    cur = torch.cuda.current_stream()
+                    ev = torch.cuda.Event()
+                    ev.record(cur)
+                    s1[r].wait_event(ev)
+                    s2[r].wait_event(ev)
+                    plans[0].reduce_scatter_apply(r, "adam", b200dp.adam_hyper(step=5), stream=s1[r])
+                    plans[1].all_gather(r, stream=s2[r])
+                    cur.wait_stream(s1[r])
+                    cur.wait_stream(s2[r])
+
+                us = time_all(n, both)
+                for r in range(n):
+                    with torch.cuda.device(r):
+                        plans[0].check(r)
+                        plans[1].check(r)
+                print(json.dumps({"n": n, "path": path, **knobs, "concurrent_rs_and_ag_us": round(us, 1)}), flush=True)
+            del plans, ctx
     best = {}
     for row in results:
         k = (row["n"], row["path"])
