@@ -61,6 +61,9 @@ class _Engine:
         numels = [t.numel() for t in per_replica[0]]
         devices = [ts[0].device.index if ts else 0 for ts in per_replica]
         plan = self.plan_for(numels, devices, bucket_bytes)
+        # MEAN = SUM x float(1/n) (Horovod's Average form).  TF's ReductionToOneDevice divides by
+        # n instead; the two agree bit for bit when n is a power of two -- every BASELINE.json
+        # config (1, 2, 4, 8) -- and can differ in the last bit otherwise.
         post = 1.0 / n if reduce_op == ReduceOp.MEAN else 1.0
         outs = []
         for r in range(n):

@@ -547,3 +547,23 @@ def test_large_plan_offsets_beyond_32_bits():
     oracle.adam_(ws, ms, vs, g[2].cpu().numpy(), step=1)
     oracle.adam_(ws, ms, vs, g[2].cpu().numpy(), step=2)
     assert np.array_equal(bits(flat_w[off2:off2 + 777].cpu().numpy()), bits(ws))
+
+
+def test_bf16_gradient_mode_within_stated_bound_of_fp32_oracle():
+    """bf16 wire vs the FP32 oracle: |err| <= 2^-8 * sum_i |g_i| (SURVEY 8c), every element;
+    (vs the bf16-wire oracle it is bit-exact, tested above)."""
+    numels = [100_000, 4096, 33]
+    n = 8
+    ctx, lay, plan = make_plan(numels, n, "bf16")
+    rng = np.random.default_rng(123)
+    hg = [np.concatenate([(rng.standard_normal(k) * 10.0 ** rng.integers(-4, 2)).astype(F) for k in numels])
+          for _ in range(n)]
+    for r in range(n):
+        plan.pack(r, dev(split(hg[r], numels)))
+    for r in range(n):
+        plan.allreduce(r)
+    got = read_tensors(plan, 0, numels, b200dp.BUF_REDUCED).astype(np.float64)
+    ref = oracle.addn(hg).astype(np.float64)
+    bound = 2.0 ** -8 * np.sum(np.abs(np.stack(hg)), axis=0)
+    assert np.all(np.abs(got - ref) <= bound)
+    assert np.array_equal(bits(got.astype(F)), bits(oracle.addn(hg, bf16_wire=True)))
