@@ -172,7 +172,8 @@ typedef enum {
   B2DP_TUNE_GRID_CAP = 0,    /* peer path: max blocks (<= 1024, also bounded by co-residency) */
   B2DP_TUNE_MC_GRID_CAP = 1, /* multicast path: max blocks */
   B2DP_TUNE_MC_UNROLL = 2,   /* multicast path: vectors in flight per thread (1, 2, 4) */
-  B2DP_TUNE_PEER_UNROLL = 3  /* peer path: 0 = automatic, 1 or 2 */
+  B2DP_TUNE_PEER_UNROLL = 3, /* peer path: 0 = automatic, 1 or 2 */
+  B2DP_TUNE_PEER_VEC = 4     /* peer path, f32 wire, n in {2,4,8}: 4 = 128-bit or 8 = 256-bit accesses */
 } b2dp_tune;
 int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value);
 

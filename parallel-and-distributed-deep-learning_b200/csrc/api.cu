@@ -126,6 +126,7 @@ struct b2dp_plan {
   int mc_grid_cap = 74;       // multicast path: fewer blocks contend less in the switch
   int mc_unroll = 1;
   int peer_unroll = 0;        // 0 = automatic (1 for n == 8, else 2)
+  int peer_vec = 8;           // elements per peer access: 8 (256-bit; f32 wire, n in {2,4,8}) or 4 (128-bit)
 };
 
 namespace {
@@ -224,8 +225,27 @@ int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_
 }
 
 struct Tuning {
-  int grid_cap, unroll;
+  int grid_cap, unroll, vec = 4;
 };
+
+template <int N, int OPT>
+int launch_step256(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  auto kernel = step256_kernel<N, OPT>;
+  const int grid = step_grid(kernel, r, a.nvec >> 1, 1, t.grid_cap);
+  kernel<<<grid, kStepThreads, 0, s>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return B2DP_OK;
+}
+
+template <int OPT>
+int launch_step256_n(int n, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  switch (n) {
+    case 2: return launch_step256<2, OPT>(r, a, t, s);
+    case 4: return launch_step256<4, OPT>(r, a, t, s);
+    case 8: return launch_step256<8, OPT>(r, a, t, s);
+  }
+  return fail(B2DP_ERR_INVALID, "256-bit peer kernel is built for 2, 4 and 8 ranks (got %d)", n);
+}
 
 template <int N, typename WireT, int OPT, int U>
 int launch_step_u(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
@@ -260,6 +280,7 @@ int launch_step_w(int n, const RankState& r, const StepArgs& a, const Tuning& t,
 
 template <int OPT>
 int launch_step_o(int wire, int n, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  if (wire == B2DP_F32 && t.vec == 8 && (n == 2 || n == 4 || n == 8)) return launch_step256_n<OPT>(n, r, a, t, s);
   if (wire == B2DP_F32) return launch_step_w<float, OPT>(n, r, a, t, s);
   return launch_step_w<__nv_bfloat16, OPT>(n, r, a, t, s);
 }
@@ -409,11 +430,11 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     } else if (mode == 3)
       rc = launch_gather(n, r, a, s);
     else if (opt == B2DP_OPT_ADAM)
-      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
+      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
     else if (opt == B2DP_OPT_SGDM)
-      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
+      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
     else
-      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll}, s);
+      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
     if (rc) return rc;
   }
   return B2DP_OK;
@@ -697,6 +718,10 @@ extern "C" int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value) {
     case B2DP_TUNE_MC_UNROLL:
       if (value != 1 && value != 2 && value != 4) return fail(B2DP_ERR_INVALID, "set_tuning: multicast unroll is 1, 2 or 4");
       p->mc_unroll = value;
+      return B2DP_OK;
+    case B2DP_TUNE_PEER_VEC:
+      if (value != 4 && value != 8) return fail(B2DP_ERR_INVALID, "set_tuning: peer vector width is 4 or 8 elements");
+      p->peer_vec = value;
       return B2DP_OK;
     case B2DP_TUNE_PEER_UNROLL:
       if (value < 0 || value > 2) return fail(B2DP_ERR_INVALID, "set_tuning: peer unroll is 0 (auto), 1 or 2");

@@ -698,6 +698,68 @@ step_mc_kernel(const StepArgs a) {
   flag_barrier(a.c, 1);
 }
 
+// 256-bit form of the peer-path step (f32 wire): one LDG.E.256 per peer and one STG.E.256 per
+// destination per thread -- half the NVLink requests of the 128-bit form for the same bytes.
+// Same rank-order sum and optimizer arithmetic, so results are bit-identical.
+template <int N, int OPT>
+__global__ void __launch_bounds__(kStepThreads)
+step256_kernel(const StepArgs a) {
+  flag_barrier(a.c, 0);
+  const int64_t nvec8 = a.nvec >> 1;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float sumsq = 0.0f, bad = 0.0f;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec8; q += stride) {
+    float8 g[N];
+#pragma unroll
+    for (int r = 0; r < N; ++r) g[r] = ld_stream_f8(reinterpret_cast<const float*>(a.g[r]) + q * 8);
+    float8 w, s0, s1;
+    if (OPT != B2DP_OPT_NONE) {
+      w = ld_stream_f8(a.w + q * 8);
+      s0 = ld_stream_f8(a.s0 + q * 8);
+      if (OPT == B2DP_OPT_ADAM) s1 = ld_stream_f8(a.s1 + q * 8);
+    }
+    float8 res;
+    float* pr = &res.lo.x;
+    float* pw = &w.lo.x;
+    float* p0 = &s0.lo.x;
+    float* p1 = &s1.lo.x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float acc = (&g[0].lo.x)[i];
+#pragma unroll
+      for (int r = 1; r < N; ++r) acc = __fadd_rn(acc, (&g[r].lo.x)[i]);
+      acc = __fmul_rn(acc, a.o.postscale);
+      if (a.want_stats) {
+        sumsq = fmaf(acc, acc, sumsq);
+        bad += (float)(!isfinite(acc));
+      }
+      if (OPT == B2DP_OPT_ADAM) {
+        adam_update(acc, pw[i], p0[i], p1[i], a.o);
+        pr[i] = pw[i];
+      } else if (OPT == B2DP_OPT_SGDM) {
+        sgdm_update(acc, pw[i], p0[i], a.o);
+        pr[i] = pw[i];
+      } else {
+        pr[i] = acc;
+      }
+    }
+    if (OPT == B2DP_OPT_ADAM) {
+      st_f8(a.s0 + q * 8, s0);
+      st_f8(a.s1 + q * 8, s1);
+    } else if (OPT == B2DP_OPT_SGDM && a.o.mu != 0.0f) {
+      st_f8(a.s0 + q * 8, s0);
+    }
+    if (N > 1 && a.push) {
+#pragma unroll
+      for (int r = 0; r < N; ++r) st_f8(a.out[r] + q * 8, res);
+    } else {
+      st_f8(a.w + q * 8, res);
+    }
+  }
+  if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
+  flag_barrier(a.c, 1);
+}
+
 // all-gather alone: push this rank's weight slice into every rank's weight buffer
 // (the PS "pull" of imagenet-resnet50-ps.py:75-82 when the step is run as two launches).
 template <int N>

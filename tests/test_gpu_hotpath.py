@@ -567,3 +567,32 @@ def test_bf16_gradient_mode_within_stated_bound_of_fp32_oracle():
     bound = 2.0 ** -8 * np.sum(np.abs(np.stack(hg)), axis=0)
     assert np.all(np.abs(got - ref) <= bound)
     assert np.array_equal(bits(got.astype(F)), bits(oracle.addn(hg, bf16_wire=True)))
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_256_bit_peer_kernel_is_bit_identical(golden, n):
+    """B2DP_TUNE_PEER_VEC=8 selects the LDG.256/STG.256 form of the peer-path step: same sums, same
+    optimizer arithmetic, so the golden answers (n=4) and the 128-bit kernel's results (any n) hold."""
+    numels = [int(x) for x in golden["numels"]]
+    ng = golden["grads"].shape[1]
+    res = []
+    for vec in (4, 8):
+        ctx, lay, plan = make_plan(numels, n, bucket_bytes=4096)
+        plan.set_tuning(peer_vec=vec)
+        w0 = dev(split(golden["w0"], numels))
+        for r in range(n):
+            plan.load_weights(r, w0)
+        for s in range(3):
+            for r in range(n):
+                plan.pack(r, dev(split(golden["grads"][s, r % ng], numels)))
+            for r in range(n):
+                plan.step(r, "adam", b200dp.adam_hyper(lr=float(golden["lrs"][s]), step=s + 1, want_stats=True))
+        for r in range(n):
+            plan.pack(r, dev(split(golden["grads"][0, r % ng], numels)))
+        for r in range(n):
+            plan.allreduce(r)
+        res.append((read_tensors(plan, n - 1, numels), read_tensors(plan, 0, numels, b200dp.BUF_REDUCED)))
+    assert np.array_equal(bits(res[0][0]), bits(res[1][0])) and np.array_equal(bits(res[0][1]), bits(res[1][1]))
+    if n == ng:
+        assert np.array_equal(bits(res[1][0]), bits(golden["adam_w_f32"]))
+        assert np.array_equal(bits(res[1][1]), bits(golden["sum_f32"][0]))

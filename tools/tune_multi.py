@@ -86,7 +86,8 @@ def main():
             configs = [("multicast", dict(mc_unroll=u, mc_grid_cap=c)) for u, c in itertools.product((1, 2, 4), (37, 74, 148, 296))]
             configs += [("peer", dict(peer_unroll=u, grid_cap=c)) for u, c in itertools.product((1, 2), (74, 148, 296, 592))]
         else:   # the chosen geometry only, plus the two halves of the step on their own
-            configs = [("multicast", dict(mc_unroll=1, mc_grid_cap=c)) for c in (74, 148)] + [("peer", dict(peer_unroll=0, grid_cap=296))]
+            configs = [("multicast", dict(mc_unroll=1, mc_grid_cap=74)), ("peer", dict(peer_unroll=0, grid_cap=296, peer_vec=4))]
+            configs += [("peer", dict(peer_unroll=0, grid_cap=c, peer_vec=8)) for c in (148, 296)]
         for path, knobs in configs:
             plan.set_path(path)
             plan.set_tuning(**knobs)
@@ -105,7 +106,7 @@ def main():
         del plan, ctx
     # Can the two directions overlap better than the fused kernel manages?  Run the two halves
     # CONCURRENTLY (two plans, so each has its own flag words; two streams per device).
-    if os.environ.get("TUNE_CONCURRENT", "1") == "1":
+    if os.environ.get("TUNE_CONCURRENT", "0") == "1":
         for n in [x for x in (8,) if x <= ndev]:
             ctx = b200dp.Context.local(list(range(n)))
             ctx.set_timeout(5.0)
