@@ -112,3 +112,38 @@ def test_out_of_range_queries():
         L.bucket_info(1)
     with pytest.raises(b200dp.B200dpError):
         L.tensor_offset(2)
+
+
+# ---------------------------------------------------------------- property-based (hypothesis)
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=150, deadline=None)
+@given(numels=st.lists(st.integers(min_value=0, max_value=20000), min_size=0, max_size=40),
+       nranks=st.integers(min_value=1, max_value=8),
+       bucket_bytes=st.sampled_from([0, 1, 1024, 4096, 65536, 1 << 20]),
+       wire=st.sampled_from(["f32", "bf16"]))
+def test_layout_invariants(numels, nranks, bucket_bytes, wire):
+    """Whatever the tensor list: the C layout equals the restatement; tensors are ordered,
+    128-byte aligned, disjoint and inside their bucket; buckets tile the flat range; every
+    rank's slices are equal, 256-element multiples, and add up to the state shard."""
+    L = b200dp.Layout(numels, nranks=nranks, wire=wire, bucket_bytes=bucket_bytes)
+    offsets, bucket_of, buckets, total = py_layout(numels, nranks, bucket_bytes)
+    assert L.total_elems == total and L.num_buckets == len(buckets)
+    assert [L.tensor_offset(k) for k in range(len(numels))] == offsets
+    cursor, shard, prev_end = 0, 0, 0
+    for b in range(L.num_buckets):
+        info = L.bucket_info(b)
+        assert info["offset"] == cursor and info["elems"] % (nranks * 256) == 0
+        assert info["slice"] * nranks == info["elems"] and info["shard_off"] == shard
+        if bucket_bytes > 0 and info["count"] > 1:   # only a single oversized tensor may exceed the limit
+            assert 4 * sum(numels[info["first"]:info["first"] + info["count"]]) <= bucket_bytes
+        cursor += info["elems"]
+        shard += info["slice"]
+    assert cursor == L.total_elems and shard == L.shard_elems
+    for k, n in enumerate(numels):
+        off = L.tensor_offset(k)
+        assert off % 32 == 0 and off >= prev_end
+        prev_end = off + n
+        info = L.bucket_info(L.tensor_bucket(k))
+        assert info["offset"] <= off and off + n <= info["offset"] + info["elems"]
