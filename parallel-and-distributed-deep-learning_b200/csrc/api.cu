@@ -6,6 +6,8 @@
 
 #include <unistd.h>
 
+#include <nvtx3/nvToolsExt.h>  // header-only; does nothing unless a profiler injects itself
+
 #include "kernels.cuh"
 
 using namespace b2dp;
@@ -33,6 +35,13 @@ struct DeviceGuard {
 };
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// NVTX range around every hot-path entry point, so an nsys/ncu timeline shows pack / step /
+// all-reduce as named host ranges (the reference has no tracing of its own).
+struct Range {
+  explicit Range(const char* name) { nvtxRangePushA(name); }
+  ~Range() { nvtxRangePop(); }
+};
 
 // Byte map of a rank's peer-mappable block.
 struct BlockMap {
@@ -368,6 +377,7 @@ int fill_opt(int opt, const b2dp_hyper* h, float postscale, OptScalars* o) {
 // mode 0: fused step (push), 1: reduce-scatter + apply only, 2: all-reduce, 3: all-gather only
 int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper* h, float postscale, int mode,
                    void* stream) {
+  Range nvtx_range("b2dp::collective");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
   RankState& r = *rp;
@@ -734,6 +744,7 @@ extern "C" int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value) {
 // ------------------------------------------------------------------------- the hot path
 extern "C" int b2dp_pack(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads,
                          int32_t grad_dtype, float prescale, void* stream) {
+  Range nvtx_range("b2dp::pack");
   RankState* r = nullptr;
   if (int rc = get_rank(p, dev, &r)) return rc;
   if (grad_dtype != B2DP_F32) return fail(B2DP_ERR_INVALID, "pack: gradients must be f32 (got dtype %d)", grad_dtype);
@@ -751,6 +762,7 @@ extern "C" int b2dp_load_weights(b2dp_plan* p, int32_t dev, const void* const* w
 
 extern "C" int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t which, void* const* outs,
                            void* stream) {
+  Range nvtx_range("b2dp::unpack");
   RankState* r = nullptr;
   if (int rc = get_rank(p, dev, &r)) return rc;
   size_t off;
@@ -769,6 +781,7 @@ extern "C" int b2dp_unpack(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t wh
 // place (no bucket copy at all); otherwise pack followed by the fused collective step.
 extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads, int32_t grad_dtype,
                               float prescale, int32_t opt, const b2dp_hyper* hyper, void* stream) {
+  Range nvtx_range("b2dp::pack_step");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
   if (opt != B2DP_OPT_ADAM && opt != B2DP_OPT_SGDM) return fail(B2DP_ERR_INVALID, "pack_step: optimizer must be ADAM or SGDM");
@@ -850,6 +863,7 @@ extern "C" int b2dp_allreduce(b2dp_plan* p, int32_t dev, int32_t bucket, float p
 // B2DP_BUF_REDUCED; b2dp_unpack(B2DP_BUF_REDUCED) then hands it out per variable, which is
 // what model.save() (imagenet-resnet50-mirror.py:83-86) needs from a sharded optimizer.
 extern "C" int b2dp_gather_state(b2dp_plan* p, int32_t dev, int32_t which, void* stream) {
+  Range nvtx_range("b2dp::gather_state");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
   RankState& r = *rp;
@@ -889,6 +903,7 @@ extern "C" int b2dp_gather_state(b2dp_plan* p, int32_t dev, int32_t which, void*
 }
 
 extern "C" int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t root, void* stream) {
+  Range nvtx_range("b2dp::broadcast");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
   RankState& r = *rp;
@@ -933,6 +948,7 @@ extern "C" int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t 
 
 extern "C" int b2dp_allreduce_small(b2dp_plan* p, int32_t dev, const float* in, float* out, int32_t count,
                                     float postscale, void* stream) {
+  Range nvtx_range("b2dp::allreduce_small");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
   RankState& r = *rp;
