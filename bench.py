@@ -406,6 +406,10 @@ def run_b200dp(args):
     step_med_ms, step_avg_ms = time_region(only_step, reps)
     sep_step_ms = step_avg_ms
     pack_med_ms, pack_avg_ms = time_region(only_pack, reps)
+    # the same per-step call once more after the board has idled for a second: directly behind
+    # ~800 W of convolution work the memory system runs a few percent slower (tools/investigate_n1.py)
+    time.sleep(1.0)
+    idle_med_ms, _ = time_region(pack_and_step, reps)
     plan.check(0)
 
     ar_med_ms = None
@@ -478,7 +482,7 @@ def run_b200dp(args):
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
                     "algorithmic_bytes_per_launch": nvl_bytes, "us_per_launch": step_avg_ms * 1e3, "traffic": None}
     busbw = (S / (step_avg_ms * 1e-3)) * 2 * (n - 1) / n / 1e9 if n > 1 else 0.0
-    hot_path = {"us_per_step_call_median": hot_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
+    hot_path = {"us_per_step_call_median": hot_med_ms * 1e3, "us_per_step_call_after_1s_idle": idle_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
                 "us_separate_apply_kernel_avg": sep_step_ms * 1e3, "us_separate_pack_kernel_avg": pack_avg_ms * 1e3, "share_of_train_step": hot_avg_ms / ms_step,
                 "allreduce_busbw_gbs": busbw, "busbw_vs_900": busbw / 900.0,
                 "pack_hbm_gbs": (4 + (2 if args.wire == "bf16" else 4)) * N_ELEMS / (pack_avg_ms * 1e-3) / 1e9,
