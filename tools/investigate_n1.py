@@ -35,6 +35,19 @@ def time_us(fn, reps=30):
     return e0.elapsed_time(e1) / reps * 1e3
 
 
+_copy_src = None
+
+
+def copy_gbs():
+    """torch copy of 512 MiB -> 512 MiB (the same kind of figure as MEASURED_PEAKS.json's hbm_gbs)."""
+    global _copy_src
+    if _copy_src is None:
+        _copy_src = (torch.empty(1 << 27, device="cuda"), torch.empty(1 << 27, device="cuda"))
+    a, b = _copy_src
+    us = time_us(lambda: b.copy_(a), reps=20)
+    return 2 * a.numel() * 4 / us / 1e3
+
+
 def main():
     torch.backends.cudnn.benchmark = True
     torch.backends.cudnn.allow_tf32 = True
@@ -59,7 +72,7 @@ def main():
         views.append(flat[o:o + k])
         o += k
     p_flat = b200dp.ptr_array(views)
-    print("cold start, contiguous grads : %.1f us   [%s]" % (time_us(mk(p_flat)), clock()))
+    print("cold start, contiguous grads : %.1f us   copy %.0f GB/s   [%s]" % (time_us(mk(p_flat)), copy_gbs(), clock()))
     for _ in range(8):
         st(x, y)
     torch.cuda.synchronize()
@@ -70,9 +83,23 @@ def main():
     al = sorted(set(g.data_ptr() % 256 for g in grads))
     print("autograd grad pointer alignment mod 256:", al[:8], "count of distinct 2MB pages:",
           len(set(g.data_ptr() >> 21 for g in grads)))
-    for _ in range(8):
-        st(x, y)
-    print("again, autograd grads : %.1f us   [%s]" % (time_us(mk(b200dp.ptr_array([p.grad for p in st.params]))), clock()))
+    for rounds in range(5):
+        for _ in range(8):
+            st.last_loss = st(x, y).detach()
+        torch.cuda.synchronize()
+        gr = [p.grad for p in st.params]
+        wbuf = plan.tensor(0, b200dp.BUF_WEIGHTS)
+        vbuf = plan.tensor(0, b200dp.BUF_STATE1)
+        gcat = torch.cat([g.flatten() for g in gr])
+        tiny = 1.1754944e-38
+        print("   loss %s  non-finite w: %d  g: %d   denormal v: %d  g: %d  zero g: %d" % (
+            float(st.last_loss) if hasattr(st, "last_loss") else "?", int((~torch.isfinite(wbuf)).sum()),
+            int((~torch.isfinite(gcat)).sum()), int(((vbuf != 0) & (vbuf.abs() < tiny)).sum()),
+            int(((gcat != 0) & (gcat.abs() < tiny)).sum()), int((gcat == 0).sum())))
+        print("after %d steps, autograd grads : %.1f us   contiguous: %.1f us   copy %.0f GB/s   [%s]" % (
+            16 + 8 * rounds, time_us(mk(b200dp.ptr_array(gr))), time_us(mk(p_flat)), copy_gbs(), clock()))
+    w_ptr, _ = plan.buffer_ptr(0, b200dp.BUF_WEIGHTS)
+    print("W at", hex(w_ptr), " S0 at", hex(plan.buffer_ptr(0, b200dp.BUF_STATE0)[0]), " S1 at", hex(plan.buffer_ptr(0, b200dp.BUF_STATE1)[0]))
 
 
 if __name__ == "__main__":
