@@ -65,14 +65,15 @@ class Layout:
             raise ValueError(L.b2dp_last_error().decode())
         check(rc)
         self._h = h
+        self._destroy = L.b2dp_layout_destroy   # bound now: module globals may be gone at interpreter exit
         self.numels = numels
         self.nranks = int(nranks)
         self.wire = wire_id
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
-            _lib.load().b2dp_layout_destroy(h)
+        if h and getattr(self, "_destroy", None):
+            self._destroy(h)
 
     num_tensors = property(lambda s: _lib.load().b2dp_layout_num_tensors(s._h))
     num_buckets = property(lambda s: _lib.load().b2dp_layout_num_buckets(s._h))
@@ -98,6 +99,7 @@ class Layout:
 class Context:
     def __init__(self, handle, nranks, ranks, devices, local):
         self._h = handle
+        self._destroy = _lib.load().b2dp_ctx_destroy
         self.nranks = nranks
         self.ranks = list(ranks)      # global rank of each local slot
         self.devices = list(devices)  # CUDA device of each local slot
@@ -126,8 +128,8 @@ class Context:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
-            _lib.load().b2dp_ctx_destroy(h)
+        if h and getattr(self, "_destroy", None):
+            self._destroy(h)
 
 
 class _DevMem:
@@ -170,11 +172,12 @@ class Plan:
         check(_lib.load().b2dp_plan_create(ctx._h, layout._h, ctypes.byref(h)))
         self._h = h
         self._L = _lib.load()
+        self._destroy = self._L.b2dp_plan_destroy
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
-            _lib.load().b2dp_plan_destroy(h)
+        if h and getattr(self, "_destroy", None):
+            self._destroy(h)
 
     # -- bootstrap (rank contexts) ----------------------------------------------------
     def exchange(self, session, timeout_ms=60000):

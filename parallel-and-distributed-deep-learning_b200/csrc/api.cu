@@ -129,6 +129,7 @@ struct b2dp_plan {
   BlockMap map;
   std::vector<std::unique_ptr<RankState>> rs;
   size_t block_bytes = 0;  // allocated size of every rank's block (granularity-rounded)
+  bool ctx_local = true;   // copy of ctx->local: destroy must not touch a context that died first
   int path = B2DP_PATH_PEER;
   // launch geometry knobs (b2dp_plan_set_tuning); defaults from the r01 sweeps on 8xB200
   int grid_cap = kMaxBlocks;  // peer-path blocks (also bounded by co-residency)
@@ -523,6 +524,7 @@ extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** o
     return fail(B2DP_ERR_INVALID, "plan_create: layout is cut for %d ranks, context has %d", l->nranks, c->nranks);
   auto p = std::make_unique<b2dp_plan>();
   p->ctx = c;
+  p->ctx_local = c->local;
   p->layout = *l;
   p->map = make_map(*l);
   for (int i = 0; i < c->nlocal; ++i) {
@@ -564,7 +566,7 @@ extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** o
 
 extern "C" void b2dp_plan_destroy(b2dp_plan* p) {
   if (!p) return;
-  for (auto& r : p->rs) destroy_rank(*r, p->block_bytes, p->ctx->local);
+  for (auto& r : p->rs) destroy_rank(*r, p->block_bytes, p->ctx_local);
   delete p;
 }
 
