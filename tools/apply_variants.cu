@@ -223,6 +223,19 @@ __global__ void copy_k(const float4* a, float4* b, long nvec) {
   for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) st4(b + q, ld4<0>(a + q));
 }
 
+__global__ void copy256_k(const float* a, float* b, long nvec8) {   // non-persistent, one 256-bit vector per thread
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < nvec8) st8(b + q * 8, ld8(a + q * 8));
+}
+__global__ void copy256x4_k(const float* a, float* b, long nvec8) {  // one block = 8192 elements, 4 vectors per thread
+  long base = (long)blockIdx.x * 1024 + threadIdx.x;
+  f8 v[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) if (base + j * 256 < nvec8) v[j] = ld8(a + (base + j * 256) * 8);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) if (base + j * 256 < nvec8) st8(b + (base + j * 256) * 8, v[j]);
+}
+
 template <typename F>
 float bench(const char* name, F launch, double bytes) {
   for (int i = 0; i < 5; ++i) launch();
@@ -255,6 +268,14 @@ int main() {
   const double B = 28.0 * 25583592;
   printf("SMs %d\n", sms);
   bench("copy 512MB->512MB (1R:1W)", [&] { copy_k<<<sms * 8, 256>>>((const float4*)c, (float4*)(c + (1 << 27)), 1 << 25); }, 2.0 * (1 << 29));
+  {
+    const long n8 = N / 8;   // the pack-sized copy: 102 MB -> 102 MB
+    const double CB = 8.0 * 25583592;
+    bench("copy 102MB 256-bit non-persistent 1 vec/thr", [&] { copy256_k<<<(int)((n8 + 255) / 256), 256>>>(g, w, n8); }, CB);
+    bench("copy 102MB 256-bit 4 vec/thr (pack shape)", [&] { copy256x4_k<<<(int)((n8 + 1023) / 1024), 256>>>(g, w, n8); }, CB);
+    bench("copy 102MB 128-bit persistent 8/SM", [&] { copy_k<<<sms * 8, 256>>>((const float4*)g, (float4*)w, N / 4); }, CB);
+    bench("copy 512MB 256-bit non-persistent 1 vec/thr", [&] { copy256_k<<<(1 << 24) / 256, 256>>>(c, c + (1 << 27), 1 << 24); }, 2.0 * (1 << 29));
+  }
 #define RUN(NAME, KERNEL, GRID, THREADS) bench(NAME, [&] { KERNEL<<<GRID, THREADS>>>(w, m, v, g, nvec, o); }, B)
   RUN("adam  512thr U2 grid 2/SM (library)", (apply_k<512, 2, 0, 1>), sms * 2, 512);
   RUN("adam  512thr U2 +L2::256B", (apply_k<512, 2, 1, 1>), sms * 2, 512);
