@@ -61,10 +61,11 @@ class _Engine:
         numels = [t.numel() for t in per_replica[0]]
         devices = [ts[0].device.index if ts else 0 for ts in per_replica]
         plan = self.plan_for(numels, devices, bucket_bytes)
-        # MEAN = SUM x float(1/n) (Horovod's Average form).  TF's ReductionToOneDevice divides by
-        # n instead; the two agree bit for bit when n is a power of two -- every BASELINE.json
-        # config (1, 2, 4, 8) -- and can differ in the last bit otherwise.
-        post = 1.0 / n if reduce_op == ReduceOp.MEAN else 1.0
+        # MEAN is SUM / n in TF (ReductionToOneDevice divides the AddN result by the replica count).
+        # For a power-of-two n -- every BASELINE.json config -- multiplying by float(1/n) inside
+        # the kernel gives the same bits; otherwise the sum is divided afterwards, exactly as TF does.
+        pow2 = (n & (n - 1)) == 0
+        post = 1.0 / n if (reduce_op == ReduceOp.MEAN and pow2) else 1.0
         outs = []
         for r in range(n):
             with torch.cuda.device(devices[r]):
@@ -76,6 +77,12 @@ class _Engine:
             with torch.cuda.device(devices[r]):
                 o = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in per_replica[r]]
                 plan.unpack(r, o, which=BUF_REDUCED)
+                if reduce_op == ReduceOp.MEAN and not pow2:
+                    # a device-tensor divisor: torch turns division by a host scalar into a
+                    # multiplication by its reciprocal, which is not the IEEE quotient
+                    d = torch.full((), float(n), device=o[0].device) if o else None
+                    for t in o:
+                        t.div_(d)
                 outs.append(o)
         return outs
 

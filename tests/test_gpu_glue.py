@@ -129,3 +129,15 @@ def test_bucket_pipeline_overlapped_with_backward_equals_serial_step():
     nb1, w_overlap = _train(True, 600_000)
     assert nb0 == 1 and nb1 >= 3
     assert torch.equal(w_serial.view(torch.int32), w_overlap.view(torch.int32))
+
+
+def test_batch_reduce_mean_three_replicas_divides_like_tf():
+    """n = 3 is not a power of two: MEAN must be the AddN sum DIVIDED by 3 (TF), not times float(1/3)."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    vals = [[torch.randn(5001, generator=g, device="cuda") for _ in range(3)] for _ in range(4)]
+    out = cdo.B200CrossDeviceOps().batch_reduce(cdo.ReduceOp.MEAN, [(v, None) for v in vals])
+    torch.cuda.synchronize()
+    for k in range(4):
+        ref = oracle.div_n(oracle.addn([t.cpu().numpy() for t in vals[k]]), 3)
+        for r in range(3):
+            assert np.array_equal(out[k][r].cpu().numpy().view(np.uint32), ref.view(np.uint32))
