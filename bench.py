@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--bucket-mb", type=float, default=0.0, help="bucket size in MB (0 = one bucket, the reference default)")
     ap.add_argument("--hotpath-only", action="store_true", help="time only pack+step on synthetic gradients")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity leg (tuning runs)")
+    ap.add_argument("--parity-dist", default="D1", choices=["D1", "D2", "D3"])
     ap.add_argument("--ref-batch", type=int, default=32, help="CPU arm: images per step (configs[0])")
     return ap.parse_args()
 
@@ -124,12 +126,13 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU arm
-def cpu_training_step_baseline(n_replicas, batch, steps, warmup, budget_s=150.0):
-    """The reference's CPU path restated: Keras-shaped ResNet-50 forward/backward on the host
-    cores (torch CPU; TensorFlow is absent), then the oracle's replica-order AddN over
-    n_replicas gradient copies and TF-form Adam over all 25.58M elements.  One replica's
-    batch is computed per step (a bounded sample: MirroredStrategy on CPU runs its replicas
-    on the same cores, so images/s does not grow with the replica count)."""
+def cpu_training_step_baseline(n_replicas, batch, steps, warmup):
+    """The reference's CPU path restated (imagenet-resnet50.py, and MirroredStrategy with CPU
+    replicas): every step runs forward/backward of the Keras-shaped ResNet-50 for EACH of the
+    n_replicas on the host cores, one replica after the other (torch CPU; TensorFlow is absent),
+    then the oracle's replica-order AddN over the n gradient lists and TF-form Adam over all
+    25.58M elements.  The batch is fixed: `batch` images per replica per step, a bounded sample
+    of the 256 images per replica of the GPU arm's configuration (nothing shrinks itself)."""
     import numpy as np
     import torch
     import oracle
@@ -140,29 +143,24 @@ def cpu_training_step_baseline(n_replicas, batch, steps, warmup, budget_s=150.0)
     model = harness.KerasResNet50().train()
     params = model.keras_order_params()
     g = torch.Generator().manual_seed(7)
-    x = torch.rand(batch, 3, 224, 224, generator=g) * 255.0
-    y = torch.randint(0, 1000, (batch,), generator=g)
+    xs = [torch.rand(batch, 3, 224, 224, generator=g) * 255.0 for _ in range(n_replicas)]
+    ys = [torch.randint(0, 1000, (batch,), generator=g) for _ in range(n_replicas)]
     N = sum(p.numel() for p in params)
     w = np.concatenate([p.detach().numpy().ravel() for p in params]).astype(np.float32)
     m, v = np.zeros(N, np.float32), np.zeros(N, np.float32)
-    others = [np.random.default_rng(r).standard_normal(N).astype(np.float32) * 1e-3 for r in range(1, n_replicas)]
     gsum = np.empty(N, np.float32)
     times, hot = [], []
     for it in range(warmup + steps):
-        if it == 1 and budget_s and first_dt * (warmup + steps) > budget_s and batch > 4:
-            # bounded sample: shrink the batch so the whole run fits the time budget
-            while batch > 4 and first_dt * (warmup + steps) > budget_s:
-                batch //= 2
-                first_dt /= 2
-            x, y = x[:batch], y[:batch]
         t0 = time.perf_counter()
-        for p in params:
-            p.grad = None
-        loss = torch.nn.functional.cross_entropy(model(x), y) / n_replicas
-        loss.backward()
-        g0 = np.concatenate([p.grad.numpy().ravel() for p in params])
+        grads = []
+        for r in range(n_replicas):
+            for p in params:
+                p.grad = None
+            loss = torch.nn.functional.cross_entropy(model(xs[r]), ys[r]) / n_replicas
+            loss.backward()
+            grads.append(np.concatenate([p.grad.numpy().ravel() for p in params]))
         t1 = time.perf_counter()
-        oracle.addn([g0] + others, out=gsum)
+        oracle.addn(grads, out=gsum)
         oracle.adam_(w, m, v, gsum, lr=1e-3, step=it + 1)
         t2 = time.perf_counter()
         o = 0
@@ -171,52 +169,129 @@ def cpu_training_step_baseline(n_replicas, batch, steps, warmup, budget_s=150.0)
                 p.copy_(torch.from_numpy(w[o:o + p.numel()]).view(p.shape))
                 o += p.numel()
         t3 = time.perf_counter()
-        if it == 0:
-            first_dt = t3 - t0
         if it >= warmup:
             times.append(t3 - t0)
             hot.append(t2 - t1)
     dt = sum(times) / len(times)
-    return {"images_per_s": batch / dt, "ms_per_step": dt * 1e3, "hot_path_ms": sum(hot) / len(hot) * 1e3,
-            "cores": cores, "loss": float(loss.detach()), "batch": batch}
+    return {"images_per_s": n_replicas * batch / dt, "ms_per_step": dt * 1e3, "hot_path_ms": sum(hot) / len(hot) * 1e3,
+            "cores": cores, "loss": float(loss.detach()), "batch": batch, "replicas": n_replicas}
+
+
+def cpu_sample_text(steps, warmup, batch, n):
+    return ("%d timed steps (%d warm-up), each step = %d replica(s) x %d images (a bounded sample of the 256 images per "
+            "replica of the GPU arm's workload) fwd+bwd on torch-CPU, then oracle AddN over the %d replica gradient "
+            "lists + TF-form Adam over all 25,583,592 elements; a port of the reference's CPU path "
+            "(imagenet-resnet50.py / MirroredStrategy on CPU devices): TensorFlow itself is not installable here"
+            % (steps, warmup, n, batch, n))
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_training_step_baseline(args.gpus, args.ref_batch, max(1, args.steps), max(1, args.warmup))
-    args.ref_batch = r["batch"]
-    sample = ("%d steps of one replica's batch %d (configs[0]) fwd+bwd on torch-CPU + oracle AddN over %d "
-              "replica gradients + TF-form Adam over all 25,583,592 elements; port of the reference's CPU path, "
-              "TensorFlow itself is not installable here" % (args.steps, args.ref_batch, args.gpus))
+    steps, warmup = max(1, args.steps), max(1, args.warmup)
+    r = cpu_training_step_baseline(args.gpus, args.ref_batch, steps, warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["images_per_s"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, args.gpus, cpu=True),
+        "config": workload_config(args, args.gpus),
         "cpu_baseline": {"value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                         "sample": sample, "hot_path_ms": r["hot_path_ms"]},
+                         "sample": cpu_sample_text(steps, warmup, args.ref_batch, args.gpus),
+                         "images_per_step": args.gpus * args.ref_batch, "hot_path_ms": r["hot_path_ms"],
+                         "conv_graph": "torch-CPU stand-in"},
         "e2e": {"value": r["images_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
 
 
-def workload_config(args, n, cpu=False):
+def workload_config(args, n):
+    """The workload both arms are quoted on (BASELINE.json configs[1]); what the CPU arm samples of
+    it is stated in its cpu_baseline.sample."""
     return {
         "workload": "imagenet-resnet50-mirror.py: Keras ResNet-50 (214 tensors, 25,583,592 params), synthetic "
                     "224x224x3, batch %d/GPU, Adam; gradient SUM + optimizer apply via b200dp" % args.batch,
-        "global_batch": (args.ref_batch if cpu else args.batch * n), "per_gpu_batch": args.ref_batch if cpu else args.batch,
+        "global_batch": args.batch * n, "per_gpu_batch": args.batch,
         "optimizer": args.optimizer, "wire_dtype": args.wire, "parallelism": "dp%d" % n,
         "collective_path": getattr(args, "path_used", "n/a"),
         "buckets": getattr(args, "num_buckets", 1), "overlap_with_backward": bool(args.overlap),
-        "conv_graph": "torch-CPU stand-in" if cpu else "torch+cuDNN stand-in (TF32 convs, as TF defaults)",
+        "conv_graph": "stand-in for the TF/cuDNN graph (TensorFlow absent): torch+cuDNN, TF32 convs as TF defaults, on the "
+                      "GPU arm; torch-CPU on the reference arm",
         "l2": "inputs_exceed_l2 (activations and 409 MB of w/m/v/g per step >> 126 MB L2)",
     }
 
 
 # ----------------------------------------------------------------------------- GPU arm
+class NvlinkCounters:
+    """Per-GPU NVLink data bytes (all links) from NVML's throughput counters: what actually crossed
+    the wire around a timed loop, next to the algorithmic figure the roofline uses."""
+    TX, RX, ALL_LINKS = 138, 139, 0xFFFFFFFF   # NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_{TX,RX}, KiB
+
+    def __init__(self, gpu_index):
+        self.h, self.why = None, None
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.read()
+        except Exception as e:   # counters are evidence, not the product: report why they are missing
+            self.h, self.why = None, "%s: %s" % (type(e).__name__, e)
+
+    def read(self):
+        vals = self.nv.nvmlDeviceGetFieldValues(self.h, [(self.TX, self.ALL_LINKS), (self.RX, self.ALL_LINKS)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                raise RuntimeError("nvml field %d returned %d" % (v.fieldId, v.nvmlReturn))
+            out.append(int(v.value.ullVal) * 1024)
+        return out   # [tx_bytes, rx_bytes]
+
+
+def parity_leg(args, plan, rank, local_rank, n):
+    """Untimed, before anything is measured: 3 Adam steps with the lr schedule [1e-3,1e-3,1e-4] through
+    pack_step on the collective path this line reports, on the seeded D1 gradients of SURVEY 8d, against
+    the CPU oracle -- bit-exact on the peer path, inside the per-element interval bound on the multicast
+    path -- plus NCCL's all_reduce of the same gradients inside the order-free bound."""
+    import torch
+    import torch.distributed as dist
+    from oracle import parity
+    try:
+        res = parity.run(plan, [(0, rank, local_rank)], dist_name=args.parity_dist, nccl=(n > 1),
+                         threads=max(1, host_cores() // n))
+    except Exception as e:   # a crash in the checker is a failed check, reported as such
+        import traceback
+        res = {"checked": True, "ok": False, "error": "%s: %s" % (type(e).__name__, e), "trace": traceback.format_exc()[-800:]}
+    if n > 1:
+        allres = [None] * n
+        dist.all_gather_object(allres, res)
+    else:
+        allres = [res]
+    merged = dict(allres[0])
+    merged["ok"] = all(r.get("ok") for r in allres)
+    for key in ("max_abs_err", "max_err_over_bound", "nccl_max_err_over_bound", "w_max_bound", "w_median_bound"):
+        vals = [r[key] for r in allres if key in r]
+        if vals:
+            merged[key] = max(vals)
+    if "bit_exact" in merged:
+        merged["bit_exact"] = all(r.get("bit_exact") for r in allres)
+    if "nccl_within_bound" in merged:
+        merged["nccl_within_bound"] = all(r.get("nccl_within_bound") for r in allres)
+    if "w_frac_bit_equal" in merged:
+        merged["w_frac_bit_equal"] = min(r["w_frac_bit_equal"] for r in allres if "w_frac_bit_equal" in r)
+    errs = [r["error"] for r in allres if "error" in r]
+    if errs:
+        merged["error"] = errs[0]
+    merged["ranks_checked"] = len(allres)
+    # leave the plan as a fresh one: zero optimizer state (the stepper reloads the weights itself)
+    import b200dp
+    plan.tensor(0, b200dp.BUF_STATE0).zero_()
+    plan.tensor(0, b200dp.BUF_STATE1).zero_()
+    torch.cuda.synchronize()
+    return merged
+
+
 def run_b200dp(args):
     import torch
     import torch.distributed as dist
@@ -263,6 +338,17 @@ def run_b200dp(args):
 
     args.path_used = plan.path if n > 1 else "n/a (single GPU)"
     args.num_buckets = lay.num_buckets
+    parity_res = None
+    if not args.no_parity:
+        parity_res = parity_leg(args, plan, rank, local_rank, n)
+        if not parity_res["ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": n, "parity": parity_res,
+                                  "error": "parity check against the oracle FAILED; nothing was timed"}))
+            if n > 1:
+                dist.barrier()
+                dist.destroy_process_group()
+            sys.exit(3)
     B = args.batch
     gen = torch.Generator(device=device).manual_seed(7 + rank)
     host_gen = torch.Generator().manual_seed(7 + rank)
@@ -399,11 +485,42 @@ def run_b200dp(args):
         h = b200dp.adam_hyper(step=tcount[0]) if args.optimizer == "adam" else b200dp.sgdm_hyper()
         plan.pack_step(0, grads_for_pack, args.optimizer, h)
 
+    # the same call when the framework hands over gradient buffers at NEW addresses every step (what
+    # torch's `p.grad = None` loop does): the library then re-sends its 214-entry pointer table and, at
+    # n == 1, re-resolves the tile table (resolve_tiles_kernel) inside the call
+    src_grads = grads if args.hotpath_only else [p.grad for p in stepper.params]
+    alt_flat = torch.empty(sum(numels) + 64, device=device)
+    alt, o = [], 16                         # a second copy of the gradients at different (still 64-byte aligned) addresses
+    for gsrc in src_grads:
+        alt.append(alt_flat[o:o + gsrc.numel()].copy_(gsrc.reshape(-1)))
+        o += gsrc.numel()
+    ptr_sets = [grads_for_pack, b200dp.ptr_array(alt)]
+
+    def pack_and_step_new_ptrs():
+        tcount[0] += 1
+        h = b200dp.adam_hyper(step=tcount[0]) if args.optimizer == "adam" else b200dp.sgdm_hyper()
+        plan.pack_step(0, ptr_sets[tcount[0] & 1], args.optimizer, h)
+
     reps = 30
     for _ in range(5):
         pack_and_step()
     hot_med_ms, hot_avg_ms = time_region(pack_and_step, reps)
+    refresh_med_ms, _ = time_region(pack_and_step_new_ptrs, reps)
+    pack_and_step()                          # back to the stable table
+    nvl = NvlinkCounters(local_rank) if n > 1 else None
+    nvl0 = nvl.read() if (nvl and nvl.h) else None
     step_med_ms, step_avg_ms = time_region(only_step, reps)
+    nvl_traffic = None
+    if nvl0 is not None:
+        nvl1 = nvl.read()
+        mine = torch.tensor([(nvl1[0] - nvl0[0]) / reps, (nvl1[1] - nvl0[1]) / reps], device=device, dtype=torch.float64)
+        allv = [torch.zeros_like(mine) for _ in range(n)]
+        dist.all_gather(allv, mine)
+        nvl_traffic = {"source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX, all links, around the %d-launch step loop" % reps,
+                       "tx_bytes_per_launch_per_gpu": [float(v[0]) for v in allv],
+                       "rx_bytes_per_launch_per_gpu": [float(v[1]) for v in allv]}
+    elif nvl is not None:
+        nvl_traffic = {"source": "NVML NVLink counters unavailable: %s" % nvl.why}
     sep_step_ms = step_avg_ms
     pack_med_ms, pack_avg_ms = time_region(only_pack, reps)
     # the same per-step call once more after the board has idled for a second: directly behind
@@ -480,9 +597,15 @@ def run_b200dp(args):
                     "bound": "nvlink", "achieved": achieved, "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
                     "frac": achieved / NVLINK_PEAK_GBS,
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
-                    "algorithmic_bytes_per_launch": nvl_bytes, "us_per_launch": step_avg_ms * 1e3, "traffic": None}
+                    "algorithmic_bytes_per_launch": nvl_bytes, "us_per_launch": step_avg_ms * 1e3,
+                    "traffic": (max(nvl_traffic["rx_bytes_per_launch_per_gpu"] + nvl_traffic["tx_bytes_per_launch_per_gpu"])
+                                if nvl_traffic and "rx_bytes_per_launch_per_gpu" in nvl_traffic else None),
+                    "traffic_note": "NVLink data bytes per launch on the busiest GPU and direction (NVML counters); "
+                                    "algorithmic_bytes_per_launch is the per-direction payload",
+                    "nvlink_counters": nvl_traffic}
     busbw = (S / (step_avg_ms * 1e-3)) * 2 * (n - 1) / n / 1e9 if n > 1 else 0.0
-    hot_path = {"us_per_step_call_median": hot_med_ms * 1e3, "us_per_step_call_after_1s_idle": idle_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
+    hot_path = {"us_per_step_call_median": hot_med_ms * 1e3, "us_per_step_call_after_1s_idle": idle_med_ms * 1e3,
+                "us_per_step_call_new_grad_addresses": refresh_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
                 "us_separate_apply_kernel_avg": sep_step_ms * 1e3, "us_separate_pack_kernel_avg": pack_avg_ms * 1e3, "share_of_train_step": hot_avg_ms / ms_step,
                 "allreduce_busbw_gbs": busbw, "busbw_vs_900": busbw / 900.0,
                 "pack_hbm_gbs": (4 + (2 if args.wire == "bf16" else 4)) * N_ELEMS / (pack_avg_ms * 1e-3) / 1e9,
@@ -507,13 +630,18 @@ def run_b200dp(args):
     }
     if e2e:
         line["e2e"] = e2e
-    if n == 1 and not args.no_cpu_baseline and not args.hotpath_only:
-        r = cpu_training_step_baseline(1, args.ref_batch, 3, 1)
+    if parity_res is not None:
+        line["parity"] = parity_res
+    if not args.no_cpu_baseline and not args.hotpath_only:
+        cpu_steps = 2 if n == 1 else 1
+        r = cpu_training_step_baseline(n, args.ref_batch, cpu_steps, 1)
         line["cpu_baseline"] = {
             "value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-            "sample": "3 steps (1 warm-up) of batch %d (configs[0]) fwd+bwd on torch-CPU + oracle TF-form Adam over "
-                      "25,583,592 elements" % args.ref_batch,
-            "hot_path_ms": r["hot_path_ms"]}
+            "sample": cpu_sample_text(cpu_steps, 1, args.ref_batch, n), "images_per_step": n * args.ref_batch,
+            "hot_path_ms": r["hot_path_ms"], "conv_graph": "torch-CPU stand-in"}
+        # the one ratio this library owns: the reference's CPU AddN + Adam over the same n gradient lists
+        # against the GPU per-step call (pack + fused reduce-scatter/Adam/all-gather)
+        hot_path["hot_path_vs_cpu"] = r["hot_path_ms"] * 1e3 / hot_path["us_per_step_call_median"]
     print(json.dumps(line))
     if n > 1:
         dist.barrier()

@@ -26,8 +26,17 @@
  *     one process (MirroredStrategy's shape); a *rank* context drives one (Horovod /
  *     MultiWorkerMirroredStrategy's shape, one process per GPU).  `dev` below is the index
  *     of the rank inside the context: 0..n-1 for a local context, always 0 for a rank one.
- *   - collective entry points (step, allreduce, all_gather) must be called for every rank,
- *     in the same order, like NCCL calls.
+ *   - collective entry points (step, allreduce, all_gather, reduce_scatter_apply, broadcast,
+ *     gather_state, allreduce_small) must be called for every rank, in the same order, like
+ *     NCCL calls.  Unlike NCCL communicators, ALL collectives of one plan share one block of
+ *     flag words and one per-rank epoch counter: on every rank they must be ordered on ONE
+ *     stream (or serialised with events).  Two collectives of the same plan in flight on
+ *     different streams can satisfy each other's waits and read buckets that are not packed
+ *     yet.  Use separate plans for traffic that must overlap (e.g. metrics on a side stream).
+ *   - if a cross-GPU flag wait gives up (a peer never reached the collective within the
+ *     context's timeout), the waiting blocks leave their slice untouched, the rank's status
+ *     word is set, and every later collective call of that rank returns B2DP_ERR_TIMEOUT
+ *     without launching until b2dp_plan_check has reported and cleared the condition.
  */
 #ifndef B200DP_H_
 #define B200DP_H_
@@ -156,7 +165,10 @@ int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream);
  * GPU per direction instead of 2(n-1)/n*S, at the price of the switch's own summation
  * order (parity within (n-1)*2^-24*sum|g_i|, not bitwise) -- the same trade NCCL's NVLS
  * all-reduce makes under MultiWorkerMirroredStrategy(NCCL) (-multiworkers.py:20-21).
- * f32 wire only.  Local context: multicast_create does everything (fd_out = -1).
+ * With a bf16 wire the switch accumulates the n bf16 copies in fp32 and returns the sum
+ * rounded ONCE more to bf16 (multimem.ld_reduce .acc::f32 .bf16x2): within
+ * 2^-8*|sum| + (n-1)*2^-24*sum|b_i| of the bf16-wire oracle (b_i = RNE bf16 of g_i) and
+ * 2^-7*sum|g_i| of the fp32 oracle; the weights still travel as fp32.  Local context: multicast_create does everything (fd_out = -1).
  * Rank contexts: rank 0 calls multicast_create and ships the fd to every rank; every rank
  * calls multicast_join(fd); after ALL ranks joined, every rank calls multicast_bind; after
  * ALL ranks bound, set_path(B2DP_PATH_MULTICAST). */
@@ -173,7 +185,8 @@ typedef enum {
   B2DP_TUNE_MC_GRID_CAP = 1, /* multicast path: max blocks */
   B2DP_TUNE_MC_UNROLL = 2,   /* multicast path: vectors in flight per thread (1, 2, 4) */
   B2DP_TUNE_PEER_UNROLL = 3, /* peer path: 0 = automatic, 1 or 2 */
-  B2DP_TUNE_PEER_VEC = 4     /* peer path, f32 wire, n in {2,4,8}: 4 = 128-bit or 8 = 256-bit accesses */
+  B2DP_TUNE_PEER_VEC = 4,    /* peer path, f32 wire, n in {2,4,8}: 4 = 128-bit or 8 = 256-bit accesses */
+  B2DP_TUNE_MC_BF16_GRID_CAP = 5 /* multicast path, bf16 wire: max blocks */
 } b2dp_tune;
 int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value);
 
@@ -197,7 +210,8 @@ int b2dp_pack(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grad
  * the PS push/apply/pull (-ps.py:75-82,142).  With n == 1 it is the optimizer apply
  * alone (imagenet-resnet50.py:62,67).  opt == B2DP_OPT_NONE is rejected (use allreduce).
  * hyper->want_stats: B2DP_BUF_STATS[0] = sum of squares of the reduced gradient over
- * this rank's shard, [1] = count of non-finite reduced-gradient elements. */
+ * this rank's shard of the buckets THIS CALL covers (bucket < 0: all of them, accumulated
+ * across the per-bucket launches), [1] = count of non-finite reduced-gradient elements. */
 int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp_hyper* hyper,
               void* stream);
 

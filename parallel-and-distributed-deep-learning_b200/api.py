@@ -330,9 +330,13 @@ class Plan:
         check(self._L.b2dp_gather_state(self._h, dev, which, self._stream(stream, dev)))
 
     def state_tensors(self, dev, which, like):
-        """Convenience for single-caller use (n == 1 or a local context driving every rank in
-        order is the caller's job): gather + unpack into new tensors shaped like `like`."""
+        """gather_state(which) + unpack(BUF_REDUCED) into new tensors shaped like `like`: the sharded
+        optimizer state `which` (BUF_STATE0 / BUF_STATE1) as per-variable tensors.  gather_state is
+        collective: with n > 1 every rank must make this call (a local context: call it for every
+        dev, from one thread per device or -- emulated ranks -- use gather_state for all ranks
+        first).  Overwrites BUF_REDUCED: call it between steps."""
         import torch
+        self.gather_state(dev, which)
         outs = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in like]
         self.unpack(dev, outs, which=BUF_REDUCED)
         return outs

@@ -6,10 +6,23 @@ Reference boundary: ``strategy = tf.distribute.MirroredStrategy()``
 then calls ``batch_reduce(ReduceOp.SUM, [(PerReplica grad_k, variable_k)] * 214)`` once per
 step [upstream tensorflow/python/distribute/cross_device_ops.py].
 
+Two process shapes, one class:
+  * ``B200CrossDeviceOps()`` -- one process drives every GPU (MirroredStrategy, -mirror.py:21):
+    a per-replica value is a list with one tensor per local replica;
+  * ``B200CrossDeviceOps(rank=r, nranks=n, device=d)`` -- one process per GPU
+    (MultiWorkerMirroredStrategy, imagenet-resnet50-multiworkers.py:20-25: each worker has ONE
+    local replica and the reduction runs across workers): a per-replica value is a list with the
+    single local tensor, the plan is built over a rank context and the peers are attached by fd
+    exchange on first use (a session string is agreed through ``session=`` or torch.distributed).
+    MWMS takes no ``cross_device_ops`` argument: ``swap_into(strategy)`` replaces
+    ``strategy.extended._cross_device_ops`` after construction, as SURVEY.md 8b describes.
+
 Two classes share one engine:
   * ``B200CrossDeviceOps``      -- executed and tested here: same method names, argument meaning
-    and error behaviour, with per-replica values given as lists of torch CUDA tensors (one per
-    replica) because TensorFlow is not installed on this image.
+    and error behaviour (reduce / batch_reduce / broadcast and the implementation hooks
+    reduce_implementation / batch_reduce_implementation / _all_reduce / _gather_implementation),
+    with per-replica values given as lists of torch CUDA tensors because TensorFlow is not
+    installed on this image.
   * ``make_tf_cross_device_ops()`` -- returns the real ``tf.distribute.CrossDeviceOps`` subclass
     when TensorFlow is importable (tensors cross via DLPack inside a ``tf.py_function``, since
     the hook runs while the step function is being traced).  Written against the upstream API,
@@ -40,26 +53,64 @@ class CommunicationOptions:
 
 
 class _Engine:
-    """Caches one plan per (tensor sizes, devices, bucket size) and runs pack -> allreduce -> unpack."""
+    """Caches one plan per (tensor sizes, devices, bucket size) and runs pack -> allreduce -> unpack.
+    Local mode drives every rank; rank mode drives this process's one rank of `nranks`."""
 
-    def __init__(self, wire="f32"):
+    def __init__(self, wire="f32", rank=None, nranks=None, device=None, session=None):
         self.wire = wire
         self._plans = {}
+        self.rank, self.nranks, self.device, self.session = rank, nranks, device, session
+        self._counter = 0
+        if (rank is None) != (nranks is None):
+            raise ValueError("give both rank and nranks (one process per GPU) or neither (one process, all GPUs)")
+        if rank is not None and not 0 <= rank < nranks:
+            raise ValueError("rank %d outside 0..%d" % (rank, nranks - 1))
+
+    @property
+    def rank_mode(self):
+        return self.rank is not None
+
+    def _session(self):
+        """A job-unique string every rank agrees on (for the fd exchange).  Given explicitly, or
+        agreed through torch.distributed when a process group is up."""
+        self._counter += 1
+        if self.session is None:
+            import os
+            import torch.distributed as dist
+            if not (dist.is_available() and dist.is_initialized()):
+                raise ValueError("rank-context B200CrossDeviceOps needs session=<job-unique string> or an initialised "
+                                 "torch.distributed process group to agree on one")
+            obj = ["cdo-%s-%d" % (os.environ.get("MASTER_PORT", "0"), os.getpid())]
+            dist.broadcast_object_list(obj, src=0)
+            self.session = obj[0]
+        return "%s-%d" % (self.session, self._counter)
 
     def plan_for(self, numels, devices, bucket_bytes):
         key = (tuple(numels), tuple(devices), int(bucket_bytes))
         if key not in self._plans:
-            ctx = api.Context.local(devices)
-            lay = api.Layout(numels, nranks=len(devices), wire=self.wire, bucket_bytes=bucket_bytes)
-            self._plans[key] = (ctx, lay, api.Plan(ctx, lay))
+            if self.rank_mode:
+                ctx = api.Context.rank(self.rank, self.nranks, devices[0])
+                lay = api.Layout(numels, nranks=self.nranks, wire=self.wire, bucket_bytes=bucket_bytes)
+                plan = api.Plan(ctx, lay)
+                if self.nranks > 1:
+                    plan.exchange(self._session())   # collective: every rank builds its plans in the same order
+            else:
+                ctx = api.Context.local(devices)
+                lay = api.Layout(numels, nranks=len(devices), wire=self.wire, bucket_bytes=bucket_bytes)
+                plan = api.Plan(ctx, lay)
+            self._plans[key] = (ctx, lay, plan)
         return self._plans[key][2]
 
     def all_reduce(self, per_replica, reduce_op, bucket_bytes):
-        """per_replica[r][k] = tensor k on replica r.  Returns the same structure, reduced."""
+        """per_replica[r][k] = tensor k on LOCAL replica r.  Returns the same structure, reduced
+        over all ranks of the job (= the local replicas in local mode)."""
         import torch
-        n = len(per_replica)
+        nlocal = len(per_replica)
+        n = self.nranks if self.rank_mode else nlocal
+        if self.rank_mode and nlocal != 1:
+            raise ValueError("one process per GPU: a per-replica value holds exactly one local tensor, got %d" % nlocal)
         numels = [t.numel() for t in per_replica[0]]
-        devices = [ts[0].device.index if ts else 0 for ts in per_replica]
+        devices = [ts[0].device.index if ts else (self.device or 0) for ts in per_replica]
         plan = self.plan_for(numels, devices, bucket_bytes)
         # MEAN is SUM / n in TF (ReductionToOneDevice divides the AddN result by the replica count).
         # For a power-of-two n -- every BASELINE.json config -- multiplying by float(1/n) inside
@@ -67,13 +118,13 @@ class _Engine:
         pow2 = (n & (n - 1)) == 0
         post = 1.0 / n if (reduce_op == ReduceOp.MEAN and pow2) else 1.0
         outs = []
-        for r in range(n):
+        for r in range(nlocal):
             with torch.cuda.device(devices[r]):
                 plan.pack(r, [t.contiguous() for t in per_replica[r]])
-        for r in range(n):
+        for r in range(nlocal):
             with torch.cuda.device(devices[r]):
                 plan.allreduce(r, postscale=post)
-        for r in range(n):
+        for r in range(nlocal):
             with torch.cuda.device(devices[r]):
                 o = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in per_replica[r]]
                 plan.unpack(r, o, which=BUF_REDUCED)
@@ -86,6 +137,36 @@ class _Engine:
                 outs.append(o)
         return outs
 
+    def all_gather(self, per_replica, axis):
+        """per_replica[r] = the tensor of LOCAL replica r.  Returns, per local replica, the
+        concatenation along `axis` of every rank's tensor in rank order (exact copies: each rank's
+        piece is placed in its own slice of the flat weight buffer and b2dp_all_gather pushes the
+        slices to every rank)."""
+        import torch
+        from ._lib import BUF_WEIGHTS
+        nlocal = len(per_replica)
+        n = self.nranks if self.rank_mode else nlocal
+        shape = tuple(per_replica[0].shape)
+        m = per_replica[0].numel()
+        piece = (m + 255) // 256 * 256                 # one rank slice: a multiple of the slice alignment
+        devices = [t.device.index for t in per_replica]
+        plan = self.plan_for([piece * n], devices, 0)  # a single "tensor" whose n slices are the pieces
+        ranks = [self.rank] if self.rank_mode else list(range(nlocal))
+        for r in range(nlocal):
+            with torch.cuda.device(devices[r]):
+                flat = plan.tensor(r, BUF_WEIGHTS)
+                flat[ranks[r] * piece:ranks[r] * piece + m].copy_(per_replica[r].contiguous().view(-1))
+        for r in range(nlocal):
+            with torch.cuda.device(devices[r]):
+                plan.all_gather(r)
+        outs = []
+        for r in range(nlocal):
+            with torch.cuda.device(devices[r]):
+                flat = plan.tensor(r, BUF_WEIGHTS)
+                parts = [flat[q * piece:q * piece + m].view(shape) for q in range(n)]
+                outs.append(torch.cat(parts, dim=axis) if shape else torch.stack(parts))
+        return outs
+
 
 class B200CrossDeviceOps:
     """Drop-in for tf.distribute.CrossDeviceOps on the gradient path (torch-tensor flavour).
@@ -95,8 +176,15 @@ class B200CrossDeviceOps:
     entry holding the same reduced value.
     """
 
-    def __init__(self, wire="f32"):
-        self._engine = _Engine(wire)
+    def __init__(self, wire="f32", rank=None, nranks=None, device=None, session=None):
+        self._engine = _Engine(wire, rank, nranks, device, session)
+        self._num_between_graph_workers = nranks or 1
+
+    def swap_into(self, strategy):
+        """MultiWorkerMirroredStrategy has no cross_device_ops argument (-multiworkers.py:24-25): the
+        drop-in there is replacing the object the strategy already built."""
+        strategy.extended._cross_device_ops = self
+        return strategy
 
     # -- public API, as upstream ---------------------------------------------------------
     def reduce(self, reduce_op, per_replica_value, destinations=None, options=None):
@@ -113,6 +201,12 @@ class B200CrossDeviceOps:
     def broadcast(self, tensor, destinations):
         return [tensor.to("cuda:%d" % d) for d in destinations]
 
+    def gather(self, per_replica_value, destinations=None, axis=0, options=None):
+        """CrossDeviceOps._gather: concatenates the replicas' tensors along `axis`."""
+        if not isinstance(per_replica_value, (list, tuple)) or not per_replica_value:
+            raise ValueError("gather: not a per-replica value (a non-empty list of tensors)")
+        return self._gather_implementation(per_replica_value, destinations, axis, options)
+
     # -- implementation hooks, as upstream ------------------------------------------------
     def reduce_implementation(self, reduce_op, per_replica_value, destinations, options):
         return self.batch_reduce_implementation(reduce_op, [(per_replica_value, destinations)], options)[0]
@@ -125,6 +219,29 @@ class B200CrossDeviceOps:
         per_replica = [[v[r] for v in values] for r in range(n)]
         reduced = self._engine.all_reduce(per_replica, reduce_op, options.bytes_per_pack)
         return [[reduced[r][k] for r in range(n)] for k in range(len(values))]
+
+    def _all_reduce(self, reduce_op, value, replica_id=0, options=None):
+        """Newer-TF hook (CollectiveAllReduce._all_reduce): all-reduce the calling replica's `value`
+        -- a tensor or a flat list of tensors -- across the replicas IN REPLICA CONTEXT.  With one
+        process per GPU (the MWMS shape) that is a direct collective call; in the one-process
+        shape TF's replica threads each call it and the calls meet inside the collective, which a
+        single-threaded caller cannot do: use batch_reduce there."""
+        if not self._engine.rank_mode:
+            raise ValueError("_all_reduce runs in replica context: construct B200CrossDeviceOps(rank=, nranks=) "
+                             "(one process per GPU) or use batch_reduce (one process, all GPUs)")
+        if not isinstance(reduce_op, ReduceOp):
+            reduce_op = ReduceOp(str(reduce_op).split(".")[-1].upper())
+        single = not isinstance(value, (list, tuple))
+        flat = [value] if single else list(value)
+        if options is None:
+            options = CommunicationOptions()
+        self._validate([([t], None) for t in flat])
+        reduced = self._engine.all_reduce([flat], reduce_op, options.bytes_per_pack)[0]
+        return reduced[0] if single else reduced
+
+    def _gather_implementation(self, per_replica_value, destinations, axis, options):
+        outs = self._engine.all_gather(list(per_replica_value), axis)
+        return outs
 
     @staticmethod
     def _validate(pairs):

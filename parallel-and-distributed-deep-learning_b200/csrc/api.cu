@@ -102,6 +102,10 @@ struct RankState {
   PtrTable grads, outs, weights;
   uint32_t epoch = 0;
   int num_sms = 0;
+  // verdict of the cross-GPU flag waits in pinned, mapped host memory: a kernel that gives up
+  // writes it, and the next collective call of this rank fails fast on it without a sync
+  int32_t* host_status = nullptr;      // host address
+  int32_t* host_status_dev = nullptr;  // the same word as the GPU addresses it
   // Path B: the plan's multicast object as seen by this rank
   unsigned long long mc_handle = 0, mc_va = 0;
   bool mc_owner = false, mc_joined = false, mc_bound = false;
@@ -135,6 +139,7 @@ struct b2dp_plan {
   int grid_cap = kMaxBlocks;  // peer-path blocks (also bounded by co-residency)
   int mc_grid_cap = 74;       // multicast path: fewer blocks contend less in the switch
   int mc_unroll = 1;
+  int mc_bf16_grid_cap = 148; // multicast path, bf16 wire (8 elements per request)
   int peer_unroll = 0;        // 0 = automatic (1 for n == 8, else 2)
   int peer_vec = 8;           // elements per peer access: 8 (256-bit; f32 wire, n in {2,4,8}) or 4 (128-bit)
 };
@@ -172,6 +177,17 @@ int get_rank(b2dp_plan* p, int dev, RankState** out) {
   if (!p) return fail(B2DP_ERR_INVALID, "plan is null");
   if (dev < 0 || dev >= (int)p->rs.size()) return fail(B2DP_ERR_INVALID, "dev %d outside 0..%d", dev, (int)p->rs.size() - 1);
   *out = p->rs[dev].get();
+  return B2DP_OK;
+}
+
+// A flag wait of an earlier collective gave up (the kernel wrote the pinned host word): every
+// later collective of this rank is refused until b2dp_plan_check has reported and cleared it,
+// so training cannot run on with weights that were only partly updated.
+int check_poisoned(const RankState& r) {
+  if (r.host_status && *reinterpret_cast<volatile int32_t*>(r.host_status) != 0)
+    return fail(B2DP_ERR_TIMEOUT,
+                "rank %d: an earlier collective timed out waiting for a peer; the weights of this plan are not "
+                "consistent across ranks any more (b2dp_plan_check reports and clears the condition)", r.rank);
   return B2DP_OK;
 }
 
@@ -339,11 +355,29 @@ int launch_step_mc(int opt, const RankState& r, const StepArgs& a, const Tuning&
   return launch_step_mc_o<B2DP_OPT_NONE>(r, a, t, s);
 }
 
+int launch_step_mc_bf16(int opt, const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
+  auto go = [&](auto kernel) {
+    const int grid = step_grid(kernel, r, a.nvec >> 1, 1, t.grid_cap);
+    kernel<<<grid, kStepThreads, 0, s>>>(a);
+    return cudaGetLastError();
+  };
+  cudaError_t e;
+  if (opt == B2DP_OPT_ADAM)
+    e = go(step_mc_bf16_kernel<B2DP_OPT_ADAM>);
+  else if (opt == B2DP_OPT_SGDM)
+    e = go(step_mc_bf16_kernel<B2DP_OPT_SGDM>);
+  else
+    e = go(step_mc_bf16_kernel<B2DP_OPT_NONE>);
+  if (e != cudaSuccess) return fail(B2DP_ERR_CUDA, "multicast bf16 step launch: %s", cudaGetErrorString(e));
+  return B2DP_OK;
+}
+
 int fill_comm(b2dp_plan* p, RankState& r, Comm* c) {
   const int n = p->ctx->nranks;
   for (int i = 0; i < kMaxRanks; ++i) c->flags[i] = nullptr;
   for (int i = 0; i < n; ++i) c->flags[i] = reinterpret_cast<uint32_t*>(r.base[i] + p->map.flags);
   c->status = reinterpret_cast<int32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlStatus);
+  c->host_status = r.host_status_dev;
   c->timeout_ns = (uint64_t)(p->ctx->timeout_s * 1e9);
   c->rank = r.rank;
   c->n = n;
@@ -383,10 +417,12 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
   if (int rc = get_rank(p, dev, &rp)) return rc;
   RankState& r = *rp;
   if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  if (int rc = check_poisoned(r)) return rc;
   int b0 = 0, b1 = 0;
   if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
   OptScalars o;
   if (int rc = fill_opt(opt, h, postscale, &o)) return rc;
+  bool stats_started = false;  // the first bucket launched by this call stores STATS, later ones add
   const int n = p->ctx->nranks;
   const size_t wire = p->layout.wire == B2DP_BF16 ? 2 : 4;
   cudaStream_t s = (cudaStream_t)stream;
@@ -411,6 +447,8 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     a.ticket = reinterpret_cast<uint32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlTicket);
     a.stats = reinterpret_cast<double*>(r.base[r.rank] + p->map.ctrl + kCtrlStats);
     a.want_stats = (h && h->want_stats) ? 1 : 0;
+    a.stats_add = stats_started ? 1 : 0;
+    stats_started = true;
     a.push = (mode == 1) ? 0 : 1;
     fill_comm(p, r, &a.c);
     int rc;
@@ -437,7 +475,10 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
       a.g[0] = mc + p->map.grads + slice_elem0 * wire;
       a.out[0] = reinterpret_cast<float*>(mc + out_off + slice_elem0 * 4);
       a.w = reinterpret_cast<float*>(r.base[r.rank] + out_off + slice_elem0 * 4);
-      rc = launch_step_mc(opt, r, a, Tuning{p->mc_grid_cap, p->mc_unroll}, s);
+      if (p->layout.wire == B2DP_BF16)
+        rc = launch_step_mc_bf16(opt, r, a, Tuning{p->mc_bf16_grid_cap, 1}, s);
+      else
+        rc = launch_step_mc(opt, r, a, Tuning{p->mc_grid_cap, p->mc_unroll}, s);
     } else if (mode == 3)
       rc = launch_gather(n, r, a, s);
     else if (opt == B2DP_OPT_ADAM)
@@ -459,6 +500,8 @@ void destroy_rank(RankState& r, size_t block_bytes = 0, bool local = true) {
   if (r.d_tiles_abs) cudaFree(r.d_tiles_abs);
   for (PtrTable* t : {&r.grads, &r.outs, &r.weights})
     if (t->dev) cudaFree(t->dev);
+  if (r.host_status) cudaFreeHost(r.host_status);
+  r.host_status = r.host_status_dev = nullptr;
   // local context: every rank shares one multicast handle/mapping and the owner frees it;
   // rank context: this process holds its own (created or imported) handle and mapping
   if (r.mc_handle && (r.mc_owner || !local)) mc_release(r.mc_handle, r.mc_va, block_bytes);
@@ -516,6 +559,46 @@ extern "C" int b2dp_ctx_set_timeout(b2dp_ctx* c, double seconds) {
 }
 
 // --------------------------------------------------------------------------------- plan
+namespace {
+// Builds one local rank of a plan; on any failure everything this rank already holds is
+// released before returning, so b2dp_plan_create never leaks a half-built rank.
+int build_rank(b2dp_plan* p, const b2dp_ctx* c, const b2dp_layout* l, int i, std::unique_ptr<RankState>* out) {
+  auto r = std::make_unique<RankState>();
+  r->device = c->devices[i];
+  r->rank = c->ranks[i];
+  DeviceGuard guard(r->device);
+  auto body = [&]() -> int {
+    CUDA_TRY(cudaFree(0));  // make sure the primary context exists before driver calls
+    CUDA_TRY(cudaDeviceGetAttribute(&r->num_sms, cudaDevAttrMultiProcessorCount, r->device));
+    size_t gran = 0, mgran = 0;
+    if (int rc = vmm_granularity(r->device, &gran)) return rc;
+    if (c->nranks > 1 && !c->emulated && mc_granularity(c->nranks, 1 << 21, &mgran) == B2DP_OK && mgran > gran)
+      gran = mgran;  // keep the block bindable to a multicast object
+    p->block_bytes = align_up(p->map.end, gran);
+    if (int rc = vmm_alloc(r->device, p->block_bytes, c->devices, c->nlocal, &r->own)) return rc;
+    CUDA_TRY(cudaMemset(reinterpret_cast<void*>(r->own.va), 0, p->map.end));
+    if (!l->tiles.empty()) {
+      CUDA_TRY(cudaMalloc(&r->d_tiles, sizeof(Tile) * l->tiles.size()));
+      CUDA_TRY(cudaMemcpy(r->d_tiles, l->tiles.data(), sizeof(Tile) * l->tiles.size(), cudaMemcpyHostToDevice));
+    }
+    if (c->nranks > 1 && !c->emulated) {
+      CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&r->host_status), sizeof(int32_t), cudaHostAllocMapped));
+      *r->host_status = 0;
+      CUDA_TRY(cudaHostGetDevicePointer(reinterpret_cast<void**>(&r->host_status_dev), r->host_status, 0));
+    }
+    return B2DP_OK;
+  };
+  if (int rc = body()) {
+    destroy_rank(*r);
+    return rc;
+  }
+  r->base[r->rank] = reinterpret_cast<char*>(r->own.va);
+  r->attached[r->rank] = true;
+  *out = std::move(r);
+  return B2DP_OK;
+}
+}  // namespace
+
 extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** out) {
   if (!out) return fail(B2DP_ERR_INVALID, "plan_create: out is null");
   *out = nullptr;
@@ -528,29 +611,11 @@ extern "C" int b2dp_plan_create(b2dp_ctx* c, const b2dp_layout* l, b2dp_plan** o
   p->layout = *l;
   p->map = make_map(*l);
   for (int i = 0; i < c->nlocal; ++i) {
-    auto r = std::make_unique<RankState>();
-    r->device = c->devices[i];
-    r->rank = c->ranks[i];
-    DeviceGuard guard(r->device);
-    CUDA_TRY(cudaFree(0));  // make sure the primary context exists before driver calls
-    CUDA_TRY(cudaDeviceGetAttribute(&r->num_sms, cudaDevAttrMultiProcessorCount, r->device));
-    size_t gran = 0, mgran = 0;
-    if (int rc0 = vmm_granularity(r->device, &gran)) return rc0;
-    if (c->nranks > 1 && !c->emulated && mc_granularity(c->nranks, 1 << 21, &mgran) == B2DP_OK && mgran > gran)
-      gran = mgran;  // keep the block bindable to a multicast object
-    p->block_bytes = align_up(p->map.end, gran);
-    int rc = vmm_alloc(r->device, p->block_bytes, c->devices, c->nlocal, &r->own);
-    if (rc) {
-      for (auto& q : p->rs) destroy_rank(*q);
+    std::unique_ptr<RankState> r;
+    if (int rc = build_rank(p.get(), c, l, i, &r)) {
+      for (auto& q : p->rs) destroy_rank(*q);  // ranks finished earlier; the failed one cleaned up after itself
       return rc;
     }
-    CUDA_TRY(cudaMemset(reinterpret_cast<void*>(r->own.va), 0, p->map.end));
-    if (!l->tiles.empty()) {
-      CUDA_TRY(cudaMalloc(&r->d_tiles, sizeof(Tile) * l->tiles.size()));
-      CUDA_TRY(cudaMemcpy(r->d_tiles, l->tiles.data(), sizeof(Tile) * l->tiles.size(), cudaMemcpyHostToDevice));
-    }
-    r->base[r->rank] = reinterpret_cast<char*>(r->own.va);
-    r->attached[r->rank] = true;
     p->rs.push_back(std::move(r));
   }
   if (c->local) {  // one address space: every rank sees every block at the same address
@@ -584,7 +649,9 @@ extern "C" int b2dp_plan_attach_peer(b2dp_plan* p, int32_t peer, int fd) {
   if (peer == r.rank) return B2DP_OK;
   if (r.attached[peer]) return fail(B2DP_ERR_STATE, "attach_peer: rank %d is already attached", peer);
   DeviceGuard guard(r.device);
-  if (int rc = vmm_import_fd(fd, p->map.end, r.device, &r.imported[peer])) return rc;
+  // map the exporter's WHOLE allocation (it was rounded to the multicast granularity, which can
+  // exceed this device's own allocation granularity), not just the bytes the layout uses
+  if (int rc = vmm_import_fd(fd, p->block_bytes, r.device, &r.imported[peer])) return rc;
   r.base[peer] = reinterpret_cast<char*>(r.imported[peer].va);
   r.attached[peer] = true;
   return B2DP_OK;
@@ -626,8 +693,10 @@ extern "C" int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream) {
   void* word = r->base[r->rank] + p->map.ctrl + kCtrlStatus;
   CUDA_TRY(cudaMemcpyAsync(&st, word, sizeof st, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaStreamSynchronize(s));
+  if (st == 0 && r->host_status) st = *reinterpret_cast<volatile int32_t*>(r->host_status);
   if (st != 0) {
     CUDA_TRY(cudaMemsetAsync(word, 0, sizeof st, s));
+    if (r->host_status) *reinterpret_cast<volatile int32_t*>(r->host_status) = 0;
     return fail(st, "rank %d: a cross-GPU flag wait timed out (a peer never reached the collective)", r->rank);
   }
   return B2DP_OK;
@@ -639,7 +708,6 @@ extern "C" int b2dp_plan_multicast_create(b2dp_plan* p, int* fd_out) {
   if (fd_out) *fd_out = -1;
   const int n = p->ctx->nranks;
   if (n < 2 || p->ctx->emulated) return fail(B2DP_ERR_STATE, "multicast_create: needs >= 2 distinct GPUs");
-  if (p->layout.wire != B2DP_F32) return fail(B2DP_ERR_STATE, "multicast_create: Path B carries an f32 wire only");
   if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "multicast_create: attach the peers first");
   RankState& r0 = *p->rs[0];
   if (r0.mc_handle) return fail(B2DP_ERR_STATE, "multicast_create: already created");
@@ -726,6 +794,10 @@ extern "C" int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value) {
     case B2DP_TUNE_MC_GRID_CAP:
       if (value < 1) return fail(B2DP_ERR_INVALID, "set_tuning: grid cap must be >= 1");
       p->mc_grid_cap = value;
+      return B2DP_OK;
+    case B2DP_TUNE_MC_BF16_GRID_CAP:
+      if (value < 1) return fail(B2DP_ERR_INVALID, "set_tuning: grid cap must be >= 1");
+      p->mc_bf16_grid_cap = value;
       return B2DP_OK;
     case B2DP_TUNE_MC_UNROLL:
       if (value != 1 && value != 2 && value != 4) return fail(B2DP_ERR_INVALID, "set_tuning: multicast unroll is 1, 2 or 4");
@@ -877,6 +949,7 @@ extern "C" int b2dp_gather_state(b2dp_plan* p, int32_t dev, int32_t which, void*
   else
     return fail(B2DP_ERR_INVALID, "gather_state: buffer %d is not STATE0 or STATE1", which);
   if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  if (int rc = check_poisoned(r)) return rc;
   const int n = p->ctx->nranks;
   DeviceGuard guard(r.device);
   cudaStream_t s = (cudaStream_t)stream;
@@ -919,6 +992,7 @@ extern "C" int b2dp_broadcast(b2dp_plan* p, int32_t dev, int32_t which, int32_t 
   else
     return fail(B2DP_ERR_INVALID, "broadcast: buffer %d is not WEIGHTS or REDUCED", which);
   if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  if (int rc = check_poisoned(r)) return rc;
   if (n == 1 || p->layout.total == 0) return B2DP_OK;
   DeviceGuard guard(r.device);
   StepArgs a;
@@ -959,6 +1033,7 @@ extern "C" int b2dp_allreduce_small(b2dp_plan* p, int32_t dev, const float* in, 
   if (count == 0) return B2DP_OK;
   if (!in || !out) return fail(B2DP_ERR_INVALID, "allreduce_small: null pointer");
   if (!b2dp_plan_ready(p)) return fail(B2DP_ERR_STATE, "plan has unattached peers");
+  if (int rc = check_poisoned(r)) return rc;
   const int n = p->ctx->nranks;
   DeviceGuard guard(r.device);
   cudaStream_t s = (cudaStream_t)stream;

@@ -82,6 +82,16 @@ __device__ __forceinline__ void multimem_st_f4(float4* mc, float4 v) {
                "f"(v.z), "f"(v.w)
                : "memory");
 }
+// bf16 wire through the switch: one 16-byte request returns 8 elements; the switch adds the n
+// copies in fp32 (.acc::f32) and rounds the sum once to bf16 on the way back.
+__device__ __forceinline__ uint4 multimem_ld_reduce_add_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -190,7 +200,8 @@ pack_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restr
 // waiting block can never keep the block it waits for off an SM.
 struct Comm {
   uint32_t* flags[kMaxRanks];  // flag block of every rank, as mapped on this GPU
-  int32_t* status;             // this rank's status word
+  int32_t* status;             // this rank's status word (device memory, read by b2dp_plan_check)
+  int32_t* host_status;        // the same verdict in pinned host memory: the next host call sees it without a sync
   uint64_t timeout_ns;
   uint32_t epoch;
   int32_t rank;
@@ -198,25 +209,35 @@ struct Comm {
   int32_t use_flags;           // 0: emulated ranks or n == 1 (stream order is the barrier)
 };
 
-__device__ __forceinline__ void flag_barrier(const Comm& c, int phase) {
-  if (c.use_flags) {
-    __syncthreads();  // every thread's earlier stores are ordered before the release below
-    if (threadIdx.x < (unsigned)c.n) {
-      const int peer = threadIdx.x;
-      const size_t slot = (size_t)(phase * kMaxBlocks + blockIdx.x) * kMaxRanks;
-      st_release_sys(c.flags[peer] + slot + c.rank, c.epoch);
-      const uint32_t* mine = c.flags[c.rank] + slot + peer;
-      const uint64_t t0 = global_timer_ns();
-      uint32_t spins = 0;
-      while ((int32_t)(ld_acquire_sys(mine) - c.epoch) < 0) {
-        if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > c.timeout_ns) {
-          atomicExch(c.status, (int32_t)B2DP_ERR_TIMEOUT);
-          break;
+// Returns false for the WHOLE block if any of its waits gave up.  A block whose entry barrier
+// failed must not touch its slice (the peers' buckets may not be packed yet) and must not
+// publish its exit flag (a late peer then times out too instead of completing against a rank
+// that skipped its part): the failure spreads to every rank instead of silently producing
+// weights that differ between them.
+__device__ __forceinline__ bool flag_barrier(const Comm& c, int phase) {
+  if (!c.use_flags) return true;
+  __syncthreads();  // every thread's earlier stores are ordered before the release below
+  int gave_up = 0;
+  if (threadIdx.x < (unsigned)c.n) {
+    const int peer = threadIdx.x;
+    const size_t slot = (size_t)(phase * kMaxBlocks + blockIdx.x) * kMaxRanks;
+    st_release_sys(c.flags[peer] + slot + c.rank, c.epoch);
+    const uint32_t* mine = c.flags[c.rank] + slot + peer;
+    const uint64_t t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - c.epoch) < 0) {
+      if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > c.timeout_ns) {
+        atomicExch(c.status, (int32_t)B2DP_ERR_TIMEOUT);
+        if (c.host_status) {
+          *reinterpret_cast<volatile int32_t*>(c.host_status) = (int32_t)B2DP_ERR_TIMEOUT;
+          __threadfence_system();
         }
+        gave_up = 1;
+        break;
       }
     }
-    __syncthreads();
   }
+  return __syncthreads_or(gave_up) == 0;
 }
 
 // ---- kernels (2)+(3): reduce-scatter(SUM) -> optimizer -> all-gather --------------------
@@ -240,6 +261,7 @@ struct StepArgs {
   uint32_t* ticket;          // scratch: arrival counter of the statistics reduction
   double* stats;             // out: [0] sum g^2, [1] non-finite count
   int32_t want_stats;
+  int32_t stats_add;         // 1: add to a.stats (a later bucket of the same call) instead of storing
   int32_t push;              // 1: store results to every rank (all-gather); 0: own copy only
 };
 
@@ -328,8 +350,9 @@ __device__ __forceinline__ void stats_reduce(const StepArgs& a, double sumsq, do
       b += __shfl_xor_sync(0xffffffffu, b, o);
     }
     if (lane == 0) {
-      a.stats[0] = s;
-      a.stats[1] = b;
+      // buckets of one call run in stream order, so adding here is deterministic
+      a.stats[0] = a.stats_add ? a.stats[0] + s : s;
+      a.stats[1] = a.stats_add ? a.stats[1] + b : b;
       *a.ticket = 0;
     }
   }
@@ -340,12 +363,13 @@ __device__ __forceinline__ void stats_reduce(const StepArgs& a, double sumsq, do
 template <int N, typename WireT, int OPT, int U>
 __global__ void __launch_bounds__(kStepThreads)
 step_kernel(const StepArgs a) {
-  flag_barrier(a.c, 0);  // every rank's bucket is packed; every rank may be written
+  const bool ok = flag_barrier(a.c, 0);  // every rank's bucket is packed; every rank may be written
 
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float sumsq = 0.0f;
   float bad = 0.0f;
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < a.nvec; base += stride * U) {
+  const int64_t nvec = ok ? a.nvec : 0;   // a block whose entry barrier timed out leaves its slice alone
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < nvec; base += stride * U) {
     float4 g[U][N];
     float4 w[U], s0[U], s1[U];
 #pragma unroll
@@ -413,7 +437,7 @@ step_kernel(const StepArgs a) {
   }
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
 
-  flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
+  if (ok) flag_barrier(a.c, 1);  // peers are done reading my bucket and writing my weights
 }
 
 // Statistics fold for the 256-thread non-persistent kernels: block partial -> scratch; the
@@ -463,8 +487,8 @@ __device__ __forceinline__ void block_stats_fold(const StepArgs& a, float sumsq,
       __syncthreads();
     }
     if (threadIdx.x == 0) {
-      a.stats[0] = sm[0][0];
-      a.stats[1] = sm[1][0];
+      a.stats[0] = a.stats_add ? a.stats[0] + sm[0][0] : sm[0][0];
+      a.stats[1] = a.stats_add ? a.stats[1] + sm[1][0] : sm[1][0];
       *a.ticket = 0;
     }
   }
@@ -647,11 +671,12 @@ fused_tiles_kernel(const TileAbs* __restrict__ tiles, float prescale, const Step
 template <int OPT, int U>
 __global__ void __launch_bounds__(kStepThreads)
 step_mc_kernel(const StepArgs a) {
-  flag_barrier(a.c, 0);
+  const bool ok = flag_barrier(a.c, 0);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float sumsq = 0.0f;
   float bad = 0.0f;
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < a.nvec; base += stride * U) {
+  const int64_t nvec = ok ? a.nvec : 0;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < nvec; base += stride * U) {
     float4 g[U], w[U], s0[U], s1[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -707,7 +732,70 @@ step_mc_kernel(const StepArgs a) {
   }
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
   __threadfence_system();  // multicast stores are performed everywhere before the exit flags go out
-  flag_barrier(a.c, 1);
+  if (ok) flag_barrier(a.c, 1);
+}
+
+// Path B with a bf16 wire: the gradient bucket crosses NVLink as bf16 (half the bytes of the
+// reduce-scatter), the switch accumulates the n copies in fp32 and returns the sum rounded once
+// to bf16; the weights still travel as fp32 multimem stores.  8 elements per thread per
+// iteration: one 16-byte multimem.ld_reduce, 256-bit local loads of w/m/v, two 16-byte
+// multimem.st.  a.g[0] = multicast address of this rank's bf16 slice; a.out[0] = multicast
+// address of the fp32 destination slice (weights, or the reduced-gradient buffer for OPT_NONE).
+template <int OPT>
+__global__ void __launch_bounds__(kStepThreads)
+step_mc_bf16_kernel(const StepArgs a) {
+  const bool ok = flag_barrier(a.c, 0);
+  const int64_t nvec8 = ok ? (a.nvec >> 1) : 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float sumsq = 0.0f, bad = 0.0f;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec8; q += stride) {
+    const uint4 gb = multimem_ld_reduce_add_bf16x8(reinterpret_cast<const uint4*>(a.g[0]) + q);
+    float8 w, s0, s1;
+    if (OPT != B2DP_OPT_NONE) {
+      w = ld_stream_f8(a.w + q * 8);
+      s0 = ld_stream_f8(a.s0 + q * 8);
+      if (OPT == B2DP_OPT_ADAM) s1 = ld_stream_f8(a.s1 + q * 8);
+    }
+    float g[8] = {bf16lo(gb.x), bf16hi(gb.x), bf16lo(gb.y), bf16hi(gb.y),
+                  bf16lo(gb.z), bf16hi(gb.z), bf16lo(gb.w), bf16hi(gb.w)};
+    float8 res;
+    float* pr = &res.lo.x;
+    float* pw = &w.lo.x;
+    float* p0 = &s0.lo.x;
+    float* p1 = &s1.lo.x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float acc = __fmul_rn(g[i], a.o.postscale);
+      if (a.want_stats) {
+        sumsq = fmaf(acc, acc, sumsq);
+        bad += (float)(!isfinite(acc));
+      }
+      if (OPT == B2DP_OPT_ADAM) {
+        adam_update(acc, pw[i], p0[i], p1[i], a.o);
+        pr[i] = pw[i];
+      } else if (OPT == B2DP_OPT_SGDM) {
+        sgdm_update(acc, pw[i], p0[i], a.o);
+        pr[i] = pw[i];
+      } else {
+        pr[i] = acc;
+      }
+    }
+    if (OPT == B2DP_OPT_ADAM) {
+      st_f8(a.s0 + q * 8, s0);
+      st_f8(a.s1 + q * 8, s1);
+    } else if (OPT == B2DP_OPT_SGDM && a.o.mu != 0.0f) {
+      st_f8(a.s0 + q * 8, s0);
+    }
+    if (a.push) {
+      multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + 2 * q, res.lo);
+      multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + 2 * q + 1, res.hi);
+    } else {
+      st_f8(a.w + q * 8, res);
+    }
+  }
+  if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
+  __threadfence_system();
+  if (ok) flag_barrier(a.c, 1);
 }
 
 // 256-bit form of the peer-path step (f32 wire): one LDG.E.256 per peer and one STG.E.256 per
@@ -716,8 +804,8 @@ step_mc_kernel(const StepArgs a) {
 template <int N, int OPT>
 __global__ void __launch_bounds__(kStepThreads)
 step256_kernel(const StepArgs a) {
-  flag_barrier(a.c, 0);
-  const int64_t nvec8 = a.nvec >> 1;
+  const bool ok = flag_barrier(a.c, 0);
+  const int64_t nvec8 = ok ? (a.nvec >> 1) : 0;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float sumsq = 0.0f, bad = 0.0f;
   for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec8; q += stride) {
@@ -769,7 +857,7 @@ step256_kernel(const StepArgs a) {
     }
   }
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);
-  flag_barrier(a.c, 1);
+  if (ok) flag_barrier(a.c, 1);
 }
 
 // all-gather alone: push this rank's weight slice into every rank's weight buffer
@@ -777,7 +865,7 @@ step256_kernel(const StepArgs a) {
 template <int N>
 __global__ void __launch_bounds__(kStepThreads)
 gather_kernel(const StepArgs a) {
-  flag_barrier(a.c, 0);
+  if (!flag_barrier(a.c, 0)) return;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride) {
     float4 v = ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q);
@@ -792,7 +880,7 @@ gather_kernel(const StepArgs a) {
 // (unicast), a.out[0] = the same slice's multicast address.
 static __global__ void __launch_bounds__(kStepThreads)
 gather_mc_kernel(const StepArgs a) {
-  flag_barrier(a.c, 0);
+  if (!flag_barrier(a.c, 0)) return;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride)
     multimem_st_f4(reinterpret_cast<float4*>(a.out[0]) + q, ld_stream_f4(reinterpret_cast<const float4*>(a.w) + q));
@@ -807,7 +895,7 @@ gather_mc_kernel(const StepArgs a) {
 template <int N>
 __global__ void __launch_bounds__(kStepThreads)
 broadcast_kernel(const StepArgs a, int root) {
-  flag_barrier(a.c, 0);  // every rank is ready to be overwritten
+  if (!flag_barrier(a.c, 0)) return;  // every rank is ready to be overwritten
   if (a.push) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < a.nvec; q += stride) {
@@ -844,7 +932,7 @@ static __global__ void __launch_bounds__(256) small_allreduce_kernel(const Small
       const float v = a.in[i];
       for (int r = 0; r < a.c.n; ++r) a.slots[r][mine + i] = v;
     }
-  flag_barrier(a.c, 0);
+  if (!flag_barrier(a.c, 0)) return;
   if (a.do_sum)
     for (int i = threadIdx.x; i < a.count; i += blockDim.x) {
       const float* base = a.slots[a.c.rank] + (size_t)a.half * kMaxRanks * kSmallMax + i;

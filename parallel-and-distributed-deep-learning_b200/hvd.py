@@ -5,8 +5,10 @@ Reference boundary: ``import horovod.tensorflow.keras as hvd`` (imagenet-resnet5
 ``hvd.DistributedOptimizer(opt)`` (:101).  One process per GPU; rank and size come from the
 launcher's environment (torchrun's RANK/WORLD_SIZE/LOCAL_RANK, or Open MPI's
 OMPI_COMM_WORLD_*, which is what horovodrun/mpirun set).  torch.distributed is used for
-rendezvous only (a session string, and the step-0 parameter broadcast); every gradient byte
-moves through the library's own kernels.
+rendezvous only (a session string); every gradient, weight and metric byte moves through the
+library's own kernels (b2dp_allreduce / b2dp_step / b2dp_broadcast / b2dp_allreduce_small).
+``hvd.callbacks`` holds the three callbacks the script constructs (:111-115) in a
+framework-neutral form: plain objects with Keras' hook names that act on an optimizer.
 
 The Keras/TensorFlow flavour with the script's exact import name is hvd_keras.py
 (unexecuted on this image: TensorFlow is absent).
@@ -75,19 +77,29 @@ def local_rank():
     return _state["local_rank"]
 
 
+def _new_plan(numels):
+    """A fresh plan over this job's ranks (collective: every rank must create it at the same point)."""
+    ctx = api.Context.rank(_state["rank"], _state["size"], _state["local_rank"])
+    lay = api.Layout(numels, nranks=_state["size"])
+    plan = api.Plan(ctx, lay)
+    if _state["size"] > 1:
+        _state["counter"] += 1
+        plan.exchange("%s-%d" % (_state["session"], _state["counter"]))
+        import torch.distributed as dist
+        dist.barrier()
+    plan._keep = (ctx, lay)
+    return plan
+
+
 def _plan_for(numels):
+    """Cached plan for the STATELESS entry points (allreduce, grouped_allreduce, broadcast_parameters):
+    they only pass data through the plan's buffers.  Anything that keeps weights or optimizer state
+    in a plan (FusedDistributedAdam) owns a plan of its own -- two optimizers over models with equal
+    parameter sizes must not alias one weight buffer and one set of Adam moments."""
     key = tuple(numels)
     if key not in _state["plans"]:
-        ctx = api.Context.rank(_state["rank"], _state["size"], _state["local_rank"])
-        lay = api.Layout(numels, nranks=_state["size"])
-        plan = api.Plan(ctx, lay)
-        if _state["size"] > 1:
-            _state["counter"] += 1
-            plan.exchange("%s-%d" % (_state["session"], _state["counter"]))
-            import torch.distributed as dist
-            dist.barrier()
-        _state["plans"][key] = (ctx, lay, plan)
-    return _state["plans"][key][2]
+        _state["plans"][key] = _new_plan(numels)
+    return _state["plans"][key]
 
 
 def _scales(average, op, prescale_factor, postscale_factor):
@@ -133,13 +145,28 @@ def allreduce(tensor, average=None, op=None, prescale_factor=1.0, postscale_fact
 
 def broadcast_parameters(params, root_rank=0):
     """hvd.broadcast_parameters / BroadcastGlobalVariablesCallback(0) (imagenet-resnet50-hvd.py:111):
-    a step-0 concern, done with torch.distributed."""
+    every rank's tensors are overwritten with the root's, through the library (load_weights ->
+    b2dp_broadcast -> unpack: one kernel over the flat buffer instead of 214 NCCL broadcasts)."""
     _need_init()
-    if _state["size"] == 1:
+    params = [p.data if hasattr(p, "data") else p for p in params]
+    if _state["size"] == 1 or not params:
         return
-    import torch.distributed as dist
-    for p in params:
-        dist.broadcast(p.data if hasattr(p, "data") else p, src=root_rank)
+    if not 0 <= root_rank < _state["size"]:
+        raise ValueError("root_rank %d outside 0..%d" % (root_rank, _state["size"] - 1))
+    from ._lib import BUF_WEIGHTS
+    plan = _plan_for([p.numel() for p in params])
+    src = [p.contiguous() for p in params]
+    plan.load_weights(0, src)
+    plan.broadcast(0, root=root_rank, which=BUF_WEIGHTS)
+    plan.unpack(0, src, which=BUF_WEIGHTS)
+    for p, c in zip(params, src):
+        if c.data_ptr() != p.data_ptr():
+            p.copy_(c)
+
+
+def broadcast_variables(variables, root_rank=0):
+    """hvd.broadcast_variables (the name horovod.tensorflow uses)."""
+    broadcast_parameters(variables, root_rank)
 
 
 class DistributedOptimizer:
@@ -184,7 +211,7 @@ class FusedDistributedAdam:
         self.params = [p for p in params if p.requires_grad]
         self.lr, self.betas, self.eps, self.t = lr, betas, eps, 0
         self._post = 1.0 / _state["size"] if op == Average else 1.0
-        self.plan = _plan_for([p.numel() for p in self.params])
+        self.plan = _new_plan([p.numel() for p in self.params])   # owns weights + Adam state: never shared
         self.plan.load_weights(0, [p.data.contiguous() for p in self.params])
         flat = self.plan.tensor(0, BUF_WEIGHTS)
         import torch
@@ -207,3 +234,127 @@ class FusedDistributedAdam:
         self.plan.pack(0, [p.grad.contiguous() for p in self.params])
         self.plan.step(0, "adam", api.adam_hyper(lr=self.lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
                                                  step=self.t, postscale=self._post))
+
+
+def _set_lr(optimizer, lr):
+    """lr of a FusedDistributedAdam (attribute) or of a torch optimizer / DistributedOptimizer (param_groups)."""
+    if hasattr(optimizer, "param_groups"):
+        for g in optimizer.param_groups:
+            g["lr"] = lr
+    else:
+        optimizer.lr = lr
+
+
+class callbacks:
+    """horovod.tensorflow.keras.callbacks, as imagenet-resnet50-hvd.py:111-115 constructs them:
+
+        hvd.callbacks.BroadcastGlobalVariablesCallback(0)
+        hvd.callbacks.MetricAverageCallback()
+        hvd.callbacks.LearningRateWarmupCallback(0.1 * hvd.size(), warmup_epochs=3, verbose=1)
+
+    Framework-neutral: objects with Keras' hook names (on_train_begin / on_epoch_begin /
+    on_batch_begin / on_batch_end / on_epoch_end) that a training loop calls in Keras' order;
+    ``set_optimizer`` plays the part of Keras' ``set_model``.  hvd_keras.py wraps the same logic
+    in keras.callbacks.Callback subclasses for a TensorFlow install."""
+
+    class _Base:
+        optimizer = None
+        params = None
+
+        def set_optimizer(self, optimizer, params=None):
+            self.optimizer, self.params = optimizer, params
+            return self
+
+        def on_train_begin(self, logs=None):
+            pass
+
+        def on_epoch_begin(self, epoch, logs=None):
+            pass
+
+        def on_batch_begin(self, batch, logs=None):
+            pass
+
+        def on_batch_end(self, batch, logs=None):
+            pass
+
+        def on_epoch_end(self, epoch, logs=None):
+            pass
+
+    class BroadcastGlobalVariablesCallback(_Base):
+        """Every rank starts from root_rank's weights (and, upstream, optimizer slots -- which are
+        all zeros at step 0 here).  Runs once, after the first batch like upstream, or at
+        on_train_begin when the variables already exist (they always do in this flavour)."""
+
+        def __init__(self, root_rank=0, device=""):
+            self.root_rank, self.broadcast_done = root_rank, False
+
+        def _broadcast(self):
+            if self.broadcast_done:
+                return
+            if hasattr(self.optimizer, "broadcast_weights"):
+                self.optimizer.broadcast_weights(self.root_rank)     # flat weight buffer, one kernel
+            elif self.params is not None:
+                broadcast_parameters(self.params, self.root_rank)
+            else:
+                raise ValueError("BroadcastGlobalVariablesCallback: set_optimizer(optimizer, params) first")
+            self.broadcast_done = True
+
+        def on_train_begin(self, logs=None):
+            self._broadcast()
+
+        def on_batch_end(self, batch, logs=None):
+            self._broadcast()
+
+    class MetricAverageCallback(_Base):
+        """Averages every numeric entry of the epoch's logs over the ranks, in sorted key order,
+        as ONE small-message all-reduce (b2dp_allreduce_small, <= 1024 metrics)."""
+
+        def __init__(self, device=""):
+            pass
+
+        def on_epoch_end(self, epoch, logs=None):
+            if not logs or _state["size"] == 1:
+                return
+            import torch
+            keys = sorted(k for k, v in logs.items() if isinstance(v, (int, float)))
+            if not keys:
+                return
+            src = torch.tensor([float(logs[k]) for k in keys], dtype=torch.float32, device="cuda")
+            out = allreduce(src, op=Average)
+            for k, v in zip(keys, out.tolist()):
+                logs[k] = v
+
+    class LearningRateWarmupCallback(_Base):
+        """Horovod's gradual warm-up (Goyal et al.): over the first warmup_epochs the learning rate
+        grows from initial_lr / size to initial_lr,
+
+            lr(epoch) = initial_lr / size * (epoch * (size - 1) / warmup_epochs + 1)
+
+        with a fractional epoch = epoch + batch / steps_per_epoch, adjusted before every batch.
+        This is why lr is a per-call argument of the apply kernel."""
+
+        def __init__(self, initial_lr, warmup_epochs=5, momentum_correction=True, steps_per_epoch=None, verbose=0):
+            self.initial_lr, self.warmup_epochs = float(initial_lr), warmup_epochs
+            self.steps_per_epoch, self.verbose = steps_per_epoch, verbose
+            self.current_epoch = 0
+
+        def multiplier(self, epoch):
+            size = _state["size"]
+            return 1.0 / size * (epoch * (size - 1) / self.warmup_epochs + 1)
+
+        def on_epoch_begin(self, epoch, logs=None):
+            self.current_epoch = epoch
+
+        def on_batch_begin(self, batch, logs=None):
+            if self.current_epoch >= self.warmup_epochs:
+                return
+            if not self.steps_per_epoch:
+                raise ValueError("LearningRateWarmupCallback needs steps_per_epoch (Keras supplies params['steps'])")
+            epoch = self.current_epoch + float(batch) / self.steps_per_epoch
+            _set_lr(self.optimizer, self.initial_lr * self.multiplier(epoch))
+
+        def on_epoch_end(self, epoch, logs=None):
+            if epoch == self.warmup_epochs - 1:
+                _set_lr(self.optimizer, self.initial_lr)
+                if self.verbose and _state["rank"] == 0:
+                    print("\nEpoch %d: finished gradual learning rate warmup to %g." % (epoch + 1, self.initial_lr))

@@ -62,43 +62,63 @@ def DistributedOptimizer(optimizer, name=None, op=Average, **kwargs):  # pragma:
 
 
 class callbacks:  # pragma: no cover
+    """keras.callbacks.Callback subclasses over the framework-neutral logic in b200dp.hvd.callbacks
+    (which is what runs and is tested on this image)."""
+
     class BroadcastGlobalVariablesCallback(keras.callbacks.Callback):
-        def __init__(self, root_rank=0):
+        def __init__(self, root_rank=0, device=""):
             super().__init__()
             self.root_rank, self.done = root_rank, False
 
         def on_batch_end(self, batch, logs=None):
             if self.done or size() == 1:
                 return
-            import torch.distributed as dist
-            for v in self.model.variables:
-                t = _to_torch(tf.convert_to_tensor(v))
-                dist.broadcast(t, src=self.root_rank)
+            import torch
+            vs = list(self.model.variables) + list(self.model.optimizer.variables())
+            ts = [_to_torch(tf.convert_to_tensor(v)).clone() for v in vs]
+            _core.broadcast_parameters(ts, self.root_rank)      # load_weights -> b2dp_broadcast -> unpack
+            torch.cuda.synchronize()
+            for v, t in zip(vs, ts):
                 v.assign(_to_tf(t))
             self.done = True
 
     class MetricAverageCallback(keras.callbacks.Callback):
+        def __init__(self, device=""):
+            super().__init__()
+            self._core = _core.callbacks.MetricAverageCallback()
+
         def on_epoch_end(self, epoch, logs=None):
-            if logs and size() > 1:
-                for k in sorted(logs):
-                    logs[k] = float(allreduce(tf.constant([logs[k]], tf.float32), op=Average)[0])
+            self._core.on_epoch_end(epoch, logs)                # one b2dp_allreduce_small over the sorted keys
 
     class LearningRateWarmupCallback(keras.callbacks.Callback):
         """lr ramps from initial_lr/size to initial_lr over warmup_epochs (the run-time lr change
         that makes lr a per-call argument of the apply kernel)."""
 
-        def __init__(self, initial_lr, warmup_epochs=5, verbose=0, steps_per_epoch=None):
+        class _KerasLr:
+            def __init__(self, cb):
+                self._cb = cb
+
+            def __setattr__(self, name, value):
+                if name == "lr":
+                    self._cb.model.optimizer.learning_rate.assign(value)
+                else:
+                    object.__setattr__(self, name, value)
+
+        def __init__(self, initial_lr, warmup_epochs=5, momentum_correction=True, steps_per_epoch=None, verbose=0):
             super().__init__()
-            self.initial_lr, self.warmup_epochs, self.verbose, self.steps = initial_lr, warmup_epochs, verbose, steps_per_epoch
-            self.epoch = 0
+            self._core = _core.callbacks.LearningRateWarmupCallback(initial_lr, warmup_epochs, momentum_correction,
+                                                                    steps_per_epoch, verbose)
+            self._core.set_optimizer(self._KerasLr(self))
+
+        def on_train_begin(self, logs=None):
+            if not self._core.steps_per_epoch:
+                self._core.steps_per_epoch = self.params.get("steps")
 
         def on_epoch_begin(self, epoch, logs=None):
-            self.epoch = epoch
+            self._core.on_epoch_begin(epoch, logs)
 
         def on_batch_begin(self, batch, logs=None):
-            if self.epoch >= self.warmup_epochs:
-                return
-            steps = self.steps or self.params.get("steps") or 1
-            e = self.epoch + batch / steps
-            lr = self.initial_lr / size() * (e * (size() - 1) / self.warmup_epochs + 1)
-            self.model.optimizer.learning_rate.assign(lr)
+            self._core.on_batch_begin(batch, logs)
+
+        def on_epoch_end(self, epoch, logs=None):
+            self._core.on_epoch_end(epoch, logs)

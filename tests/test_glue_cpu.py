@@ -74,3 +74,81 @@ def test_hvd_bootstrap_two_processes_gloo():
         p.join(30)
     for rank, ok, same_session in res:
         assert ok and same_session
+
+
+def test_learning_rate_warmup_follows_horovods_formula(monkeypatch):
+    """hvd.callbacks.LearningRateWarmupCallback(0.1 * size, warmup_epochs=3) (imagenet-resnet50-hvd.py:115):
+    lr(epoch) = initial_lr / size * (epoch * (size - 1) / warmup_epochs + 1), fractional epochs,
+    set before every batch; exactly initial_lr once warm-up is over."""
+    from b200dp import hvd
+
+    class Opt:
+        lr = -1.0
+
+    for size in (1, 2, 8):
+        monkeypatch.setitem(hvd._state, "size", size)
+        monkeypatch.setitem(hvd._state, "init", True)
+        init = 0.1 * size
+        cb = hvd.callbacks.LearningRateWarmupCallback(init, warmup_epochs=3, steps_per_epoch=10, verbose=0)
+        opt = Opt()
+        cb.set_optimizer(opt)
+        seen = []
+        for epoch in range(5):
+            cb.on_epoch_begin(epoch)
+            for batch in range(10):
+                cb.on_batch_begin(batch)
+                seen.append(opt.lr)
+            cb.on_epoch_end(epoch)
+        for i, lr in enumerate(seen[:30]):
+            e = i / 10.0
+            assert lr == pytest.approx(init / size * (e * (size - 1) / 3 + 1), rel=1e-12)
+        assert seen[0] == pytest.approx(0.1)                 # starts at the single-worker rate
+        assert all(lr == init for lr in seen[30:])           # and stays at initial_lr afterwards
+        assert all(b >= a for a, b in zip(seen, seen[1:]))
+    with pytest.raises(ValueError, match="steps_per_epoch"):
+        cb2 = hvd.callbacks.LearningRateWarmupCallback(0.1, warmup_epochs=3).set_optimizer(Opt())
+        cb2.on_batch_begin(0)
+
+    # a torch-style optimizer: param_groups carry the rate
+    class TorchLike:
+        param_groups = [{"lr": 0.0}, {"lr": 0.0}]
+
+    monkeypatch.setitem(hvd._state, "size", 4)
+    t = TorchLike()
+    cb = hvd.callbacks.LearningRateWarmupCallback(0.4, warmup_epochs=2, steps_per_epoch=4).set_optimizer(t)
+    cb.on_epoch_begin(1)
+    cb.on_batch_begin(2)
+    assert [g["lr"] for g in t.param_groups] == [pytest.approx(0.4 / 4 * (1.5 * 3 / 2 + 1))] * 2
+
+
+def test_metric_average_and_broadcast_callbacks_are_noops_on_one_rank(monkeypatch):
+    from b200dp import hvd
+    monkeypatch.setitem(hvd._state, "size", 1)
+    monkeypatch.setitem(hvd._state, "init", True)
+    logs = {"loss": 1.5, "accuracy": 0.25, "name": "x"}
+    hvd.callbacks.MetricAverageCallback().on_epoch_end(0, logs)
+    assert logs == {"loss": 1.5, "accuracy": 0.25, "name": "x"}
+    cb = hvd.callbacks.BroadcastGlobalVariablesCallback(0).set_optimizer(object(), params=[])
+    cb.on_train_begin()
+    assert cb.broadcast_done
+    with pytest.raises(ValueError, match="set_optimizer"):
+        hvd.callbacks.BroadcastGlobalVariablesCallback(0).on_batch_end(0)
+
+
+def test_rank_context_cross_device_ops_argument_errors():
+    with pytest.raises(ValueError, match="both rank and nranks"):
+        cdo.B200CrossDeviceOps(rank=0)
+    with pytest.raises(ValueError, match="outside"):
+        cdo.B200CrossDeviceOps(rank=3, nranks=2)
+    ops = cdo.B200CrossDeviceOps()
+    with pytest.raises(ValueError, match="replica context"):
+        ops._all_reduce(cdo.ReduceOp.SUM, None)
+
+    class FakeExtended:
+        _cross_device_ops = None
+
+    class FakeStrategy:
+        extended = FakeExtended()
+
+    s = FakeStrategy()
+    assert ops.swap_into(s) is s and s.extended._cross_device_ops is ops

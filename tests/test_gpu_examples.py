@@ -1,4 +1,5 @@
-"""The example scripts (torch flavours of imagenet-resnet50-mirror.py and -hvd.py) run end to end."""
+"""The example scripts (torch flavours of imagenet-resnet50-mirror.py, -hvd.py, -multiworkers.py and -ps.py:
+all five BASELINE.json configurations have a runnable shape) run end to end."""
 import os
 import subprocess
 import sys
@@ -34,3 +35,36 @@ def test_hvd_example_two_ranks_torchrun():
     out = run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
                "127.0.0.1", "--master-port", "29577", "examples/resnet50_hvd_torch.py", "--steps", "2", "--batch", "4"])
     assert "mean loss over 2 ranks" in out and "All done for rank 1" in out
+
+
+def test_multiworkers_example_single_worker():
+    out = run([sys.executable, "examples/resnet50_multiworkers_torch.py", "--steps", "2", "--batch", "4"])
+    assert "All done for worker 0" in out
+
+
+def test_ps_example_single_gpu_saves_a_partitioned_checkpoint(tmp_path):
+    path = str(tmp_path / "ps.npz")
+    out = run([sys.executable, "examples/resnet50_ps_torch.py", "--steps", "2", "--batch", "4", "--gpus", "1", "--save", path])
+    assert "workers hold identical weights: True" in out and "Saving model to" in out
+    import numpy as np
+    names = set(np.load(path).keys())
+    assert "conv1_conv/kernel" in names and "optimizer/iterations" in names
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("fused", [False, True])
+def test_multiworkers_example_two_workers(fused):
+    out = run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+               "127.0.0.1", "--master-port", "29578", "examples/resnet50_multiworkers_torch.py", "--steps", "2",
+               "--batch", "4"] + (["--fused"] if fused else []))
+    assert "worker 1 holds the same weights as worker 0: True" in out and "All done for worker 1" in out
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+def test_ps_example_two_gpus(tmp_path):
+    path = str(tmp_path / "ps2.npz")
+    out = run([sys.executable, "examples/resnet50_ps_torch.py", "--steps", "2", "--batch", "4", "--gpus", "2", "--save", path])
+    assert "workers hold identical weights: True" in out
+    import numpy as np
+    names = set(np.load(path).keys())
+    assert "dense/kernel/part_0" in names and "dense/kernel/part_1" in names and "optimizer/dense/kernel/m/part_1" in names

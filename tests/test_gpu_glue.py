@@ -141,3 +141,73 @@ def test_batch_reduce_mean_three_replicas_divides_like_tf():
         ref = oracle.div_n(oracle.addn([t.cpu().numpy() for t in vals[k]]), 3)
         for r in range(3):
             assert np.array_equal(out[k][r].cpu().numpy().view(np.uint32), ref.view(np.uint32))
+
+
+def test_gather_concatenates_replicas_along_any_axis():
+    """CrossDeviceOps._gather_implementation (newer TF): exact copies, rank order, any axis (3
+    emulated replicas on cuda:0; -0.0 and NaN payloads survive because nothing is added)."""
+    ops = cdo.B200CrossDeviceOps()
+    g = torch.Generator(device="cuda").manual_seed(9)
+    vals = [torch.randn(5, 7, generator=g, device="cuda") for _ in range(3)]
+    vals[1][0, 0] = -0.0
+    for axis in (0, 1):
+        outs = ops.gather(vals, axis=axis)
+        torch.cuda.synchronize()
+        want = torch.cat(vals, dim=axis)
+        assert len(outs) == 3
+        for o in outs:
+            assert torch.equal(o.view(torch.int32), want.view(torch.int32))
+    scal = ops.gather([torch.tensor(float(r), device="cuda") for r in range(3)], axis=0)
+    assert scal[0].tolist() == [0.0, 1.0, 2.0]
+
+
+def test_rank_context_cross_device_ops_single_worker():
+    """The MWMS-shaped constructor with one worker: batch_reduce, _all_reduce (tensor and list) and
+    gather all pass through the library and return the input (SUM over one replica)."""
+    ops = cdo.B200CrossDeviceOps(rank=0, nranks=1, device=0)
+    a, b = torch.randn(1000, device="cuda"), torch.randn(3, 5, device="cuda")
+    out = ops.batch_reduce(cdo.ReduceOp.SUM, [([a], None), ([b], None)])
+    assert torch.equal(out[0][0], a) and torch.equal(out[1][0], b)
+    assert torch.equal(ops._all_reduce(cdo.ReduceOp.MEAN, a, 0, None), a)
+    red = ops._all_reduce("SUM", [a, b])
+    assert torch.equal(red[0], a) and torch.equal(red[1], b)
+    assert torch.equal(ops.gather([b], axis=0)[0], b)
+    with pytest.raises(ValueError):
+        ops.batch_reduce(cdo.ReduceOp.SUM, [([a, a], None)])     # one process per GPU: one local replica
+
+
+def test_two_fused_adam_optimizers_over_equal_shapes_do_not_alias():
+    """Two FusedDistributedAdam instances over models with the same parameter sizes (an EMA or
+    teacher copy) own separate plans: separate weights, separate Adam moments."""
+    from b200dp import hvd
+    hvd.shutdown()
+    hvd.init()
+    rng = np.random.default_rng(8)
+    shapes = [(300, 40), (40,)]
+    init = [[rng.standard_normal(s).astype(F) * 0.05 for s in shapes] for _ in range(2)]
+    models = [[torch.nn.Parameter(torch.from_numpy(x).cuda()) for x in ws] for ws in init]
+    opts = [hvd.FusedDistributedAdam(ps, lr=1e-3) for ps in models]
+    assert opts[0].plan is not opts[1].plan
+    refs = [[np.concatenate([x.ravel() for x in ws]), None, None] for ws in init]
+    for ref in refs:
+        ref[1], ref[2] = np.zeros_like(ref[0]), np.zeros_like(ref[0])
+    for step in (1, 2):
+        for i in (0, 1):
+            gs = [rng.standard_normal(s).astype(F) * 1e-2 for s in shapes]
+            for p, g in zip(models[i], gs):
+                p.grad = torch.from_numpy(g).cuda()
+            opts[i].step()
+            oracle.adam_(refs[i][0], refs[i][1], refs[i][2], np.concatenate([g.ravel() for g in gs]), lr=1e-3, step=step)
+    torch.cuda.synchronize()
+    for i in (0, 1):
+        got = np.concatenate([p.detach().cpu().numpy().ravel() for p in models[i]])
+        assert np.array_equal(got.view(np.uint32), refs[i][0].view(np.uint32)), "model %d" % i
+
+
+def test_hvd_broadcast_parameters_single_rank_is_a_noop():
+    from b200dp import hvd
+    hvd.shutdown()
+    hvd.init()
+    p = torch.nn.Parameter(torch.arange(10.0, device="cuda"))
+    hvd.broadcast_parameters([p], root_rank=0)
+    assert p.tolist() == list(range(10))

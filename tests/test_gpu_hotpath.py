@@ -596,3 +596,40 @@ def test_256_bit_peer_kernel_is_bit_identical(golden, n):
     if n == ng:
         assert np.array_equal(bits(res[1][0]), bits(golden["adam_w_f32"]))
         assert np.array_equal(bits(res[1][1]), bits(golden["sum_f32"][0]))
+
+
+# ------------------------------------------------------------------ statistics across buckets
+@pytest.mark.parametrize("n", [1, 2, 4])
+@pytest.mark.parametrize("call", ["step", "pack_step", "reduce_scatter_apply"])
+def test_stats_cover_every_bucket_of_the_call(n, call):
+    """want_stats with a multi-bucket plan: one call launches one kernel per bucket, and
+    B2DP_BUF_STATS must hold the sum over ALL of them (summed over ranks = the oracle's sum of
+    squares of the whole reduced gradient), including a non-finite element planted in bucket 0."""
+    numels = [5000, 64, 3000, 9001, 128, 7000, 2048, 4100]
+    N = sum(numels)
+    ctx, lay, plan = make_plan(numels, n, bucket_bytes=20000)
+    assert lay.num_buckets >= 4
+    rng = np.random.default_rng(11)
+    for plant_inf in (False, True):
+        hg = [(rng.standard_normal(N) * 1e-2).astype(F) for _ in range(n)]
+        if plant_inf:
+            hg[0][17] = np.inf                      # tensor 0 -> bucket 0
+        gts = [dev(split(g, numels)) for g in hg]
+        h = b200dp.adam_hyper(step=1, want_stats=True)
+        if call == "pack_step" and n == 1:
+            plan.pack_step(0, gts[0], "adam", h)
+        else:
+            for r in range(n):
+                plan.pack(r, gts[r])
+            for r in range(n):
+                getattr(plan, "step" if call == "pack_step" else call)(r, "adam", h)
+        torch.cuda.synchronize()
+        stats = np.stack([plan.tensor(r, b200dp.BUF_STATS).cpu().numpy() for r in range(n)])
+        gsum = oracle.addn(hg)
+        if plant_inf:
+            assert stats[:, 1].sum() == 1, stats
+            assert np.isinf(stats[:, 0].sum())
+        else:
+            want = oracle.sumsq(gsum)
+            assert abs(stats[:, 0].sum() - want) <= 1e-6 * want, (stats, want)   # tolerance: rel 1e-6
+            assert stats[:, 1].sum() == 0

@@ -168,3 +168,63 @@ def test_empty_input_is_a_noop():
     e = np.zeros(0, dtype=F)
     assert oracle.addn([e, e]).size == 0
     oracle.adam_(e, e.copy(), e.copy(), e.copy())
+
+
+# ------------------------------------------------------------------ bounds for order-free paths
+@pytest.mark.parametrize("dist", ["D1", "D3"])
+@pytest.mark.parametrize("order", ["reversed", "pairwise", "float64"])
+def test_interval_bound_holds_for_any_summation_order(dist, order):
+    """oracle/bounds.py: a sum taken in another order (what the NVSwitch or NCCL may do) stays inside
+    (n-1)*2^-24*sum|g_i| of the rank-order sum, and three Adam steps driven by it stay inside the
+    per-element interval AdamBound propagates -- while that interval remains a few ulp of |w| wide."""
+    import torch
+    from oracle import bounds, synth
+    numels = [64, 1000, 7, 0, 1027, 512, 40000]
+    N, n = sum(numels), 8
+    w = ((torch.rand(N, generator=torch.Generator().manual_seed(42)) - 0.5) * 0.1).numpy()
+    m, v = np.zeros(N, F), np.zeros(N, F)
+    w2, m2, v2 = w.copy(), m.copy(), v.copy()
+    tr = bounds.AdamBound(N)
+    for s, lr in enumerate((1e-3, 1e-3, 1e-4)):
+        hg = [g.numpy() for g in synth.all_ranks(dist, n, s, numels)]
+        gs = oracle.addn(hg)
+        if order == "reversed":
+            gh = oracle.addn(hg[::-1])
+        elif order == "float64":
+            gh = np.sum(np.stack(hg).astype(np.float64), axis=0).astype(F)
+        else:
+            a = [(hg[2 * i] + hg[2 * i + 1]).astype(F) for i in range(4)]
+            gh = ((a[0] + a[1]).astype(F) + (a[2] + a[3]).astype(F)).astype(F)
+        B = bounds.sum_bound_f32(hg)
+        assert np.all(np.abs(gh.astype(np.float64) - gs) <= B)
+        mo, vo = m.copy(), v.copy()
+        oracle.adam_(w, m, v, gs, lr=lr, step=s + 1)
+        oracle.adam_(w2, m2, v2, gh, lr=lr, step=s + 1)
+        tr.step(gs, B, mo, vo, m, v, w, oracle.adam_alpha(lr, 0.9, 0.999, s + 1))
+    for got, ref, bound in ((w2, w, tr.Ew), (m2, m, tr.Em + 1e-38), (v2, v, tr.Ev + 1e-38)):
+        c = bounds.check(got, ref, bound, "x")
+        assert c["ok"] and c["max_err_over_bound"] <= 1.0, c
+    assert np.median(tr.Ew) <= 1e-7          # informative: |w| <= 0.05 has ulp 3.7e-9
+    # and it is not vacuous: a gradient error 1000 times the bound is caught
+    w3, m3, v3 = w.copy(), m.copy(), v.copy()
+    oracle.adam_(w3, m3, v3, (gs + 1000 * B).astype(F), lr=1e-3, step=4)
+    w4, m4, v4 = w.copy(), m.copy(), v.copy()
+    mo, vo = m.copy(), v.copy()
+    oracle.adam_(w4, m4, v4, gs, lr=1e-3, step=4)
+    tr.step(gs, B, mo, vo, m4, v4, w4, oracle.adam_alpha(1e-3, 0.9, 0.999, 4))
+    assert not bounds.check(w3, w4, tr.Ew, "x")["ok"]
+
+
+def test_synthetic_gradients_are_reproducible_and_shaped_as_specified():
+    from oracle import synth
+    numels = [64, 0, 1000, 4096]
+    a = synth.all_ranks("D3", 2, 1, numels)
+    b = synth.all_ranks("D3", 2, 1, numels)
+    assert all(np.array_equal(x.numpy(), y.numpy()) for x, y in zip(a, b))
+    d3 = a[0].numpy()
+    nz = np.abs(d3[d3 != 0])
+    assert 0 < (d3 == 0).mean() < 0.05 and nz.min() >= 2.0 ** -24.01 and nz.max() <= 2.0 ** 8.01
+    d2 = synth.all_ranks("D2", 2, 0, numels)
+    assert d2[0].mean() > 9e3 and d2[1].mean() < -9e3
+    d1 = synth.rank_grad("D1", 0, 0, numels).numpy()
+    assert abs(d1.std() - 1e-3) < 1e-4 and not np.array_equal(d1, synth.rank_grad("D1", 1, 0, numels).numpy())

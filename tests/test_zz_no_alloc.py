@@ -57,6 +57,10 @@ def test_two_calls_in_a_row_match_the_plan_based_entry_point():
     # new entry point: caller-owned arrays (allocated here, by the caller, up front)
     w, m, v = w0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
     stats = torch.zeros(2, dtype=torch.float64, device=dev)
+    # and the CPU oracle on the same inputs, so the new entry point is held to the reference
+    # arithmetic directly and not only through another kernel of this library
+    import oracle
+    w_orc, m_orc, v_orc = w0.cpu().numpy().copy(), np.zeros(n, np.float32), np.zeros(n, np.float32)
 
     for step, lr in ((1, 1e-3), (2, 1e-4)):
         g = torch.randn(n, generator=gen, device=dev) * 1e-2
@@ -78,6 +82,12 @@ def test_two_calls_in_a_row_match_the_plan_based_entry_point():
         ref_stats = plan.tensor(0, b200dp.BUF_STATS).cpu().numpy()
         for name, got, ref in (("w", w, ref_w), ("m", m, ref_m), ("v", v, ref_v)):
             assert torch.equal(got.view(torch.int32), ref.view(torch.int32)), "%s differs at step %d" % (name, step)
+        if step == 1:                   # finite inputs: bit-exact against the oracle's TF-form Adam as well
+            oracle.adam_(w_orc, m_orc, v_orc, g.cpu().numpy(), lr=lr, step=step)
+            for name, got, ref in (("w", w, w_orc), ("m", m, m_orc), ("v", v, v_orc)):
+                assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.view(np.uint32)), \
+                    "%s differs from the oracle at step %d" % (name, step)
+            assert abs(stats.cpu().numpy()[0] - oracle.sumsq(g.cpu().numpy())) <= 1e-6 * oracle.sumsq(g.cpu().numpy())
         got_stats = stats.cpu().numpy()
         if step == 1:
             assert abs(got_stats[0] - ref_stats[0]) <= 1e-6 * ref_stats[0]     # tolerance: rel 1e-6
