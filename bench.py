@@ -185,9 +185,37 @@ def cpu_sample_text(steps, warmup, batch, n):
             % (steps, warmup, n, batch, n))
 
 
+def clean_cpu_env():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use every
+    host core, so it runs in a child process without the launcher's variables."""
+    env = dict(os.environ)
+    for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE",
+              "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    env["B2DP_CPU_CHILD"] = "1"
+    env["CUDA_VISIBLE_DEVICES"] = ""
+    return env
+
+
+def cpu_baseline_subprocess(n, batch, steps, warmup):
+    """cpu_training_step_baseline in a fresh interpreter (all host cores, no CUDA context, none of the
+    launcher's thread limits); returns its result dict."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--gpus", str(n), "--steps", str(steps),
+           "--warmup", str(warmup), "--ref-batch", str(batch)]
+    out = subprocess.run(cmd, capture_output=True, text=True, env=clean_cpu_env(), cwd=ROOT, timeout=3000)
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    if out.returncode != 0 or not lines:
+        raise RuntimeError("CPU baseline child failed: rc %d\n%s" % (out.returncode, out.stderr[-2000:]))
+    return json.loads(lines[-1])
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return
+    if os.environ.get("B2DP_CPU_CHILD") != "1" and (os.environ.get("OMP_NUM_THREADS") or "TORCHELASTIC_RUN_ID" in os.environ):
+        line = cpu_baseline_subprocess(args.gpus, args.ref_batch, args.steps, args.warmup)   # same arm, clean environment
+        print(json.dumps(line))
         return
     steps, warmup = max(1, args.steps), max(1, args.warmup)
     r = cpu_training_step_baseline(args.gpus, args.ref_batch, steps, warmup)
@@ -556,6 +584,23 @@ def run_b200dp(args):
         nccl_med_ms, _ = time_region(lambda: dist.all_reduce(buf), reps)
         del buf
 
+    # b2dp_adam_apply_noalloc (the entry point for callers that cannot allocate) on the same 25.58M elements
+    noalloc_ms = None
+    if n == 1 and args.optimizer == "adam":
+        na = [torch.zeros(N_ELEMS, device=device) for _ in range(3)]
+        na_g = torch.randn(N_ELEMS, device=device) * 1e-3
+        na_stats = torch.zeros(2, dtype=torch.float64, device=device)
+        na_t = [0]
+
+        def noalloc_call():
+            na_t[0] += 1
+            b200dp.adam_apply_noalloc(na[0], na[1], na[2], na_g, b200dp.adam_hyper(step=na_t[0]), na_stats)
+
+        for _ in range(3):
+            noalloc_call()
+        noalloc_ms = time_region(noalloc_call, reps)[0]
+        del na, na_g
+
     e2e = None
     if step_e2e is not None:
         ms_e2e = timed(step_e2e, args.steps, args.warmup)
@@ -611,6 +656,9 @@ def run_b200dp(args):
                 "pack_hbm_gbs": (4 + (2 if args.wire == "bf16" else 4)) * N_ELEMS / (pack_avg_ms * 1e-3) / 1e9,
                 "elems_per_rank": elems_per_rank}
     hot_path.update(other)
+    if noalloc_ms is not None:
+        hot_path["us_adam_apply_noalloc"] = noalloc_ms * 1e3
+        hot_path["adam_apply_noalloc_hbm_gbs"] = 28 * N_ELEMS / (noalloc_ms * 1e-3) / 1e9
     if ar_med_ms:
         hot_path["allreduce_only_us"] = ar_med_ms * 1e3
         hot_path["allreduce_only_busbw_gbs"] = (S / (ar_med_ms * 1e-3)) * 2 * (n - 1) / n / 1e9
@@ -634,14 +682,10 @@ def run_b200dp(args):
         line["parity"] = parity_res
     if not args.no_cpu_baseline and not args.hotpath_only:
         cpu_steps = 2 if n == 1 else 1
-        r = cpu_training_step_baseline(n, args.ref_batch, cpu_steps, 1)
-        line["cpu_baseline"] = {
-            "value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-            "sample": cpu_sample_text(cpu_steps, 1, args.ref_batch, n), "images_per_step": n * args.ref_batch,
-            "hot_path_ms": r["hot_path_ms"], "conv_graph": "torch-CPU stand-in"}
+        line["cpu_baseline"] = cpu_baseline_subprocess(n, args.ref_batch, cpu_steps, 1)["cpu_baseline"]
         # the one ratio this library owns: the reference's CPU AddN + Adam over the same n gradient lists
         # against the GPU per-step call (pack + fused reduce-scatter/Adam/all-gather)
-        hot_path["hot_path_vs_cpu"] = r["hot_path_ms"] * 1e3 / hot_path["us_per_step_call_median"]
+        hot_path["hot_path_vs_cpu"] = line["cpu_baseline"]["hot_path_ms"] * 1e3 / hot_path["us_per_step_call_median"]
     print(json.dumps(line))
     if n > 1:
         dist.barrier()

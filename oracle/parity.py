@@ -65,9 +65,13 @@ def run(plan, locals_, dist_name="D1", average=False, nccl=False, threads=None, 
         hg = [g.cpu().numpy() for g in dg]
         h = b200dp.adam_hyper(lr=lr, step=s + 1, postscale=post)
         emulated = len(set(ctx.devices)) < len(ctx.devices)   # ranks share one GPU: no kernel may wait on another
-        for dev, rank, cdev in locals_:
+        # every local rank's gradient on its own GPU BEFORE the first collective is issued: a
+        # cross-device copy queued behind a kernel that waits for its peers would never run
+        gl = [dg[rank] if cdev == gen_dev.index else dg[rank].to("cuda:%d" % cdev) for _dev, rank, cdev in locals_]
+        for _dev, _rank, cdev in locals_:
+            torch.cuda.synchronize(cdev)
+        for (dev, rank, cdev), g in zip(locals_, gl):
             with torch.cuda.device(cdev):
-                g = dg[rank] if cdev == gen_dev.index else dg[rank].to("cuda:%d" % cdev)
                 if emulated:
                     plan.pack(dev, _views(g, numels))
                 else:
@@ -97,7 +101,7 @@ def run(plan, locals_, dist_name="D1", average=False, nccl=False, threads=None, 
         adam_(w_ref, m_ref, v_ref, gsum, lr=lr, step=s + 1)
         if track is not None:
             track.step(gsum, B, m_old, v_old, m_ref, v_ref, w_ref, adam_alpha(lr, 0.9, 0.999, s + 1))
-        del dg
+        del dg, gl
 
     for _dev, _rank, cdev in locals_:
         torch.cuda.synchronize(cdev)

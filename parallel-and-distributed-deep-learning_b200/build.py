@@ -2,6 +2,7 @@
 import os
 import subprocess
 import sys
+import time
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
@@ -32,8 +33,26 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return OUT
     cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SOURCES
+    t0 = time.time()
     subprocess.check_call(cmd, cwd=CSRC)
+    _record(cmd, time.time() - t0)
     return OUT
+
+
+def _record(cmd, seconds):
+    """Leaves a note of the compile that produced the library (command, seconds, host) where a
+    GPU-box run brings it back from: gpurun_out/build_record.json.  Best effort."""
+    try:
+        import json
+        import platform
+        root = os.path.dirname(HERE)
+        d = os.path.join(root, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "build_record.json"), "w") as f:
+            json.dump({"cmd": cmd, "cwd": CSRC, "seconds": round(seconds, 2), "output": OUT,
+                       "bytes": os.path.getsize(OUT), "host": platform.node(), "when": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime())}, f)
+    except Exception:
+        pass
 
 
 if __name__ == "__main__":

@@ -84,9 +84,14 @@ BlockMap make_map(const b2dp_layout& l) {
   return m;
 }
 
-struct PtrTable {          // device copy of a caller's K-pointer array, re-sent only on change
-  void** dev = nullptr;
-  std::vector<const void*> host;
+// A caller's K-pointer array as the kernels use it: the plan's tile table with those pointers
+// resolved (TileAbs), rebuilt by one small kernel only when the array changes.  Everything is
+// allocated when the plan is created; the hot path never allocates.
+struct PtrTable {
+  std::vector<const void*> host;   // the array the resolved table was built from
+  TileAbs* abs = nullptr;          // one entry per tile of the layout
+  bool valid = false;
+  void** dev = nullptr;            // device copy of the array; only for K > kParamPtrs
 };
 
 struct RankState {
@@ -97,8 +102,6 @@ struct RankState {
   char* base[kMaxRanks] = {};  // every rank's block as addressable from this rank's GPU
   bool attached[kMaxRanks] = {};
   Tile* d_tiles = nullptr;
-  TileAbs* d_tiles_abs = nullptr;  // tiles with the gradient pointers resolved (n == 1 fused kernel)
-  bool abs_valid = false;
   PtrTable grads, outs, weights;
   uint32_t epoch = 0;
   int num_sms = 0;
@@ -106,6 +109,10 @@ struct RankState {
   // writes it, and the next collective call of this rank fails fast on it without a sync
   int32_t* host_status = nullptr;      // host address
   int32_t* host_status_dev = nullptr;  // the same word as the GPU addresses it
+  // multi-bucket pack_step: bucket b+1 is packed on `side` while bucket b's collective step runs
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_start = nullptr;
+  std::vector<cudaEvent_t> ev_packed;  // one per bucket
   // Path B: the plan's multicast object as seen by this rank
   unsigned long long mc_handle = 0, mc_va = 0;
   bool mc_owner = false, mc_joined = false, mc_bound = false;
@@ -161,15 +168,27 @@ int check_device(int device) {
   return B2DP_OK;
 }
 
-int sync_table(PtrTable& t, const void* const* ptrs, int K, cudaStream_t s, bool* changed = nullptr) {
-  if (changed) *changed = false;
-  if (K == 0) return B2DP_OK;
-  if (!t.dev) CUDA_TRY(cudaMalloc(&t.dev, sizeof(void*) * K));
-  if ((int)t.host.size() == K && memcmp(t.host.data(), ptrs, sizeof(void*) * K) == 0) return B2DP_OK;
-  if (changed) *changed = true;
+// Brings `t.abs` up to date with the caller's pointer array.  Unchanged array (the common case:
+// frameworks keep gradient buffers at stable addresses): nothing is launched.  Changed: one
+// resolve kernel; for up to kParamPtrs tensors the pointers ride in its launch parameters.
+int sync_tiles(const b2dp_layout& l, Tile* d_tiles, PtrTable& t, const void* const* ptrs, cudaStream_t s) {
+  const int K = l.K;
+  const int64_t ntiles = (int64_t)l.tiles.size();
+  if (K == 0 || ntiles == 0) return B2DP_OK;
+  if (t.valid && (int)t.host.size() == K && memcmp(t.host.data(), ptrs, sizeof(void*) * K) == 0) return B2DP_OK;
   t.host.assign(ptrs, ptrs + K);
-  // pageable source: the runtime stages it before returning, so t.host may change later
-  CUDA_TRY(cudaMemcpyAsync(t.dev, t.host.data(), sizeof(void*) * K, cudaMemcpyHostToDevice, s));
+  const unsigned grid = (unsigned)((ntiles + 255) / 256);
+  if (K <= kParamPtrs) {
+    PtrPack pk;
+    memcpy(pk.p, ptrs, sizeof(void*) * K);
+    resolve_tiles_param_kernel<<<grid, 256, 0, s>>>(d_tiles, ntiles, pk, t.abs);
+  } else {
+    // pageable source: the runtime stages it before returning, so t.host may change later
+    CUDA_TRY(cudaMemcpyAsync(t.dev, t.host.data(), sizeof(void*) * K, cudaMemcpyHostToDevice, s));
+    resolve_tiles_kernel<<<grid, 256, 0, s>>>(d_tiles, ntiles, t.dev, t.abs);
+  }
+  CUDA_TRY(cudaGetLastError());
+  t.valid = true;
   return B2DP_OK;
 }
 
@@ -213,9 +232,6 @@ int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const v
   int b0 = 0, b1 = 0;
   if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
   if (!ptrs && p->layout.K > 0) return fail(B2DP_ERR_INVALID, "tensor pointer array is null");
-  bool changed = false;
-  if (int rc = sync_table(table, ptrs, p->layout.K, s, &changed)) return rc;
-  if (changed && &table == &r.grads) r.abs_valid = false;  // the resolved tile table follows the gradient pointers
   for (int b = b0; b < b1; ++b) {
     const Bucket& bk = p->layout.buckets[b];
     if (bk.tile_count == 0) continue;
@@ -227,13 +243,13 @@ int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const v
   int64_t nt = 0;
   for (int b = b0; b < b1; ++b) nt += p->layout.buckets[b].tile_count;
   if (nt == 0) return B2DP_OK;
+  if (int rc = sync_tiles(p->layout, r.d_tiles, table, ptrs, s)) return rc;
   char* flat = r.base[r.rank] + flat_off;
   const int grid = pack_grid(r, nt);
   if (wire == B2DP_F32)
-    pack_kernel<float, DIR><<<grid, kPackThreads, 0, s>>>(r.d_tiles + t0, nt, table.dev, (float*)flat, prescale);
+    pack_kernel<float, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (float*)flat, prescale);
   else
-    pack_kernel<__nv_bfloat16, DIR><<<grid, kPackThreads, 0, s>>>(r.d_tiles + t0, nt, table.dev,
-                                                                  (__nv_bfloat16*)flat, prescale);
+    pack_kernel<__nv_bfloat16, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (__nv_bfloat16*)flat, prescale);
   CUDA_TRY(cudaGetLastError());
   return B2DP_OK;
 }
@@ -247,7 +263,13 @@ int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_
   }
   int64_t want = (nvec + (int64_t)kStepThreads * U - 1) / ((int64_t)kStepThreads * U);
   int64_t cap = std::min<int64_t>(std::max(1, std::min(kMaxBlocks, grid_cap)), (int64_t)r.num_sms * occ);
-  return (int)std::max<int64_t>(1, std::min(want, cap));
+  if (want <= cap) return (int)std::max<int64_t>(1, want);
+  // A persistent grid-stride loop runs ceil(want / grid) rounds and the last round costs a full
+  // round however few blocks still have work in it.  Take the smallest grid that needs the same
+  // number of rounds as the cap would: every block then does the same number of rounds (+-0)
+  // and no round is spent on a fraction of the grid (up to one round in ~11 at n = 2).
+  const int64_t rounds = (want + cap - 1) / cap;
+  return (int)((want + rounds - 1) / rounds);
 }
 
 struct Tuning {
@@ -256,7 +278,14 @@ struct Tuning {
 
 template <int N, int OPT>
 int launch_step256(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
-  auto kernel = step256_kernel<N, OPT>;
+  if (t.unroll == 2 && N == 2) {   // two 256-bit vectors per peer in flight per thread (tuning knob; spills for N >= 4)
+    auto kernel = step256_kernel<N, OPT, (N == 2 ? 2 : 1)>;
+    const int grid = step_grid(kernel, r, a.nvec >> 1, 2, t.grid_cap);
+    kernel<<<grid, kStepThreads, 0, s>>>(a);
+    CUDA_TRY(cudaGetLastError());
+    return B2DP_OK;
+  }
+  auto kernel = step256_kernel<N, OPT, 1>;
   const int grid = step_grid(kernel, r, a.nvec >> 1, 1, t.grid_cap);
   kernel<<<grid, kStepThreads, 0, s>>>(a);
   CUDA_TRY(cudaGetLastError());
@@ -411,7 +440,7 @@ int fill_opt(int opt, const b2dp_hyper* h, float postscale, OptScalars* o) {
 
 // mode 0: fused step (push), 1: reduce-scatter + apply only, 2: all-reduce, 3: all-gather only
 int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper* h, float postscale, int mode,
-                   void* stream) {
+                   void* stream, bool stats_continue = false) {
   Range nvtx_range("b2dp::collective");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
@@ -422,7 +451,7 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
   if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
   OptScalars o;
   if (int rc = fill_opt(opt, h, postscale, &o)) return rc;
-  bool stats_started = false;  // the first bucket launched by this call stores STATS, later ones add
+  bool stats_started = stats_continue;  // the first bucket launched by a call stores STATS, later ones add
   const int n = p->ctx->nranks;
   const size_t wire = p->layout.wire == B2DP_BF16 ? 2 : 4;
   cudaStream_t s = (cudaStream_t)stream;
@@ -497,11 +526,20 @@ void destroy_rank(RankState& r, size_t block_bytes = 0, bool local = true) {
   DeviceGuard guard(r.device);
   cudaDeviceSynchronize();
   if (r.d_tiles) cudaFree(r.d_tiles);
-  if (r.d_tiles_abs) cudaFree(r.d_tiles_abs);
-  for (PtrTable* t : {&r.grads, &r.outs, &r.weights})
+  for (PtrTable* t : {&r.grads, &r.outs, &r.weights}) {
     if (t->dev) cudaFree(t->dev);
+    if (t->abs) cudaFree(t->abs);
+    t->dev = nullptr;
+    t->abs = nullptr;
+  }
   if (r.host_status) cudaFreeHost(r.host_status);
   r.host_status = r.host_status_dev = nullptr;
+  if (r.side) cudaStreamDestroy(r.side);
+  if (r.ev_start) cudaEventDestroy(r.ev_start);
+  for (cudaEvent_t e : r.ev_packed) cudaEventDestroy(e);
+  r.side = nullptr;
+  r.ev_start = nullptr;
+  r.ev_packed.clear();
   // local context: every rank shares one multicast handle/mapping and the owner frees it;
   // rank context: this process holds its own (created or imported) handle and mapping
   if (r.mc_handle && (r.mc_owner || !local)) mc_release(r.mc_handle, r.mc_va, block_bytes);
@@ -580,6 +618,19 @@ int build_rank(b2dp_plan* p, const b2dp_ctx* c, const b2dp_layout* l, int i, std
     if (!l->tiles.empty()) {
       CUDA_TRY(cudaMalloc(&r->d_tiles, sizeof(Tile) * l->tiles.size()));
       CUDA_TRY(cudaMemcpy(r->d_tiles, l->tiles.data(), sizeof(Tile) * l->tiles.size(), cudaMemcpyHostToDevice));
+      for (PtrTable* t : {&r->grads, &r->outs, &r->weights}) {   // everything the hot path will ever need
+        CUDA_TRY(cudaMalloc(&t->abs, sizeof(TileAbs) * l->tiles.size()));
+        if (l->K > kParamPtrs) CUDA_TRY(cudaMalloc(&t->dev, sizeof(void*) * l->K));
+      }
+    }
+    if (c->nranks > 1 && !c->emulated && l->buckets.size() > 1) {
+      CUDA_TRY(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
+      CUDA_TRY(cudaEventCreateWithFlags(&r->ev_start, cudaEventDisableTiming));
+      for (size_t b = 0; b < l->buckets.size(); ++b) {
+        cudaEvent_t e = nullptr;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        r->ev_packed.push_back(e);
+      }
     }
     if (c->nranks > 1 && !c->emulated) {
       CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&r->host_status), sizeof(int32_t), cudaHostAllocMapped));
@@ -867,6 +918,25 @@ extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const v
   const bool direct = p->ctx->nranks == 1 && p->layout.wire == B2DP_F32 &&
                       (!(hyper && hyper->want_stats) || nt * kSubTiles <= kApplyMaxBlocks);
   if (!direct) {
+    RankState& r = *rp;
+    if (r.side && b1 - b0 > 1) {
+      // Several buckets, real ranks: the step of bucket b is NVLink-bound and leaves HBM idle, so
+      // bucket b+1 is packed underneath it on a side stream.  Same kernels, same arguments, same
+      // order of collectives on the caller's stream as the serial form: bit-identical results.
+      cudaStream_t s = (cudaStream_t)stream;
+      DeviceGuard guard(r.device);
+      CUDA_TRY(cudaEventRecord(r.ev_start, s));          // gradients exist; earlier steps have read the buckets
+      CUDA_TRY(cudaStreamWaitEvent(r.side, r.ev_start, 0));
+      bool stats_on = false;
+      for (int b = b0; b < b1; ++b) {
+        if (int rc = b2dp_pack(p, dev, b, grads, grad_dtype, prescale, r.side)) return rc;
+        CUDA_TRY(cudaEventRecord(r.ev_packed[b], r.side));
+        CUDA_TRY(cudaStreamWaitEvent(s, r.ev_packed[b], 0));
+        if (int rc = run_collective(p, dev, b, opt, hyper, 1.0f, 0, stream, stats_on)) return rc;
+        stats_on = true;
+      }
+      return B2DP_OK;
+    }
     if (int rc = b2dp_pack(p, dev, bucket, grads, grad_dtype, prescale, stream)) return rc;
     return b2dp_step(p, dev, bucket, opt, hyper, stream);
   }
@@ -882,15 +952,7 @@ extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const v
   }
   cudaStream_t s = (cudaStream_t)stream;
   DeviceGuard guard(r.device);
-  bool changed = false;
-  if (int rc = sync_table(r.grads, grads, p->layout.K, s, &changed)) return rc;
-  const int64_t all_tiles = (int64_t)p->layout.tiles.size();
-  if (!r.d_tiles_abs) CUDA_TRY(cudaMalloc(&r.d_tiles_abs, sizeof(TileAbs) * all_tiles));
-  if (changed || !r.abs_valid) {  // rare: frameworks keep gradient buffers at stable addresses
-    resolve_tiles_kernel<<<(unsigned)((all_tiles + 255) / 256), 256, 0, s>>>(r.d_tiles, all_tiles, r.grads.dev, r.d_tiles_abs);
-    CUDA_TRY(cudaGetLastError());
-    r.abs_valid = true;
-  }
+  if (int rc = sync_tiles(p->layout, r.d_tiles, r.grads, grads, s)) return rc;
   StepArgs a;
   memset(&a, 0, sizeof a);
   // tile offsets are flat element offsets; with one rank a shard offset equals the flat offset
@@ -902,7 +964,7 @@ extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const v
   a.ticket = reinterpret_cast<uint32_t*>(r.base[r.rank] + p->map.ctrl + kCtrlTicket);
   a.stats = reinterpret_cast<double*>(r.base[r.rank] + p->map.ctrl + kCtrlStats);
   a.want_stats = hyper->want_stats ? 1 : 0;
-  const TileAbs* tiles = r.d_tiles_abs + p->layout.buckets[b0].tile_first;
+  const TileAbs* tiles = r.grads.abs + p->layout.buckets[b0].tile_first;
   const unsigned grid = (unsigned)(nt * kSubTiles);
   if (opt == B2DP_OPT_ADAM)
     fused_tiles_kernel<B2DP_OPT_ADAM><<<grid, kApplyThreads, 0, s>>>(tiles, prescale, a);

@@ -108,21 +108,66 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// A tile with its tensor pointer already resolved (rebuilt by a resolve kernel only when the
+// caller's pointer array changes): a block's first data load then depends on ONE table load
+// instead of two (tile -> pointer table -> data).
+struct TileAbs {
+  float* ptr;        // tensor pointer + offset of the tile inside it
+  int64_t dst_off;   // flat element offset
+  uint32_t count;
+  uint32_t pad;
+};
+
+// Up to kParamPtrs tensor pointers travel to the resolve kernel as a launch parameter: no device
+// pointer table, no host->device copy, nothing to allocate when a framework hands over gradient
+// buffers at new addresses every step.
+constexpr int kParamPtrs = 448;
+struct PtrPack {
+  void* p[kParamPtrs];
+};
+
+static __global__ void resolve_tiles_param_kernel(const Tile* __restrict__ tiles, int64_t ntiles,
+                                                  const __grid_constant__ PtrPack ptrs, TileAbs* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntiles) {
+    const Tile tl = tiles[t];
+    TileAbs o;
+    o.ptr = reinterpret_cast<float*>(ptrs.p[tl.tensor]) + tl.src_off;
+    o.dst_off = tl.dst_off;
+    o.count = tl.count;
+    o.pad = 0;
+    out[t] = o;
+  }
+}
+
+static __global__ void resolve_tiles_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
+                                            TileAbs* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntiles) {
+    const Tile tl = tiles[t];
+    TileAbs o;
+    o.ptr = reinterpret_cast<float*>(ptrs[tl.tensor]) + tl.src_off;
+    o.dst_off = tl.dst_off;
+    o.count = tl.count;
+    o.pad = 0;
+    out[t] = o;
+  }
+}
+
 // ---- kernel (1): pack / unpack --------------------------------------------------------
 // One launch over the device-resident tile table; a tile is a run of <= 8192 elements
 // inside one tensor (one block each), so work is split by bytes however ragged the tensor
 // list is.  DIR 0: tensors -> flat (cast to WireT, times prescale); DIR 1: flat(f32) -> tensors.
 template <typename WireT, int DIR>
 __global__ void __launch_bounds__(kPackThreads)
-pack_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
-            WireT* __restrict__ flat, float prescale) {
+pack_kernel(const TileAbs* __restrict__ tiles, int64_t ntiles, WireT* __restrict__ flat, float prescale) {
   // One tile per block: with ~6400 short-lived blocks the hardware scheduler keeps every SM
   // busy and blocks in different phases (loading / storing) overlap, which measured ~10%
   // faster than a persistent grid-stride loop for this pure stream.
   const int64_t t = blockIdx.x;
   if (t >= ntiles) return;
-  const Tile tl = tiles[t];
-  float* tens = reinterpret_cast<float*>(ptrs[tl.tensor]) + tl.src_off;
+  const TileAbs tl = tiles[t];
+  float* tens = tl.ptr;
   WireT* fl = flat + tl.dst_off;
   const uint32_t count = tl.count;
   const uintptr_t addr = reinterpret_cast<uintptr_t>(tens);
@@ -548,35 +593,12 @@ apply1_kernel(const StepArgs a) {
 // pack -> step, so the result is bit-identical to the two-launch form.
 constexpr int kSubTiles = kTileElems / (8 * kApplyThreads);  // blocks per tile
 
-// A tile with its gradient pointer already resolved (rebuilt by resolve_tiles_kernel only
-// when the caller's pointer array changes): one dependent load per block instead of two.
-struct TileAbs {
-  const float* src;  // tensor pointer + offset of the tile inside it
-  int64_t dst_off;   // flat element offset
-  uint32_t count;
-  uint32_t pad;
-};
-
-static __global__ void resolve_tiles_kernel(const Tile* __restrict__ tiles, int64_t ntiles, void* const* __restrict__ ptrs,
-                                     TileAbs* __restrict__ out) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < ntiles) {
-    const Tile tl = tiles[t];
-    TileAbs o;
-    o.src = reinterpret_cast<const float*>(ptrs[tl.tensor]) + tl.src_off;
-    o.dst_off = tl.dst_off;
-    o.count = tl.count;
-    o.pad = 0;
-    out[t] = o;
-  }
-}
-
 template <int OPT>
 __global__ void __launch_bounds__(kApplyThreads, 5)
 fused_tiles_kernel(const TileAbs* __restrict__ tiles, float prescale, const StepArgs a) {
   const TileAbs tl = tiles[blockIdx.x / kSubTiles];
   const uint32_t e0 = ((blockIdx.x % kSubTiles) * kApplyThreads + threadIdx.x) * 8;  // element inside the tile
-  const float* tens = tl.src;
+  const float* tens = tl.ptr;
   float* w = a.w + tl.dst_off;
   float* s0 = a.s0 + tl.dst_off;
   float* s1 = a.s1 + tl.dst_off;
@@ -801,59 +823,71 @@ step_mc_bf16_kernel(const StepArgs a) {
 // 256-bit form of the peer-path step (f32 wire): one LDG.E.256 per peer and one STG.E.256 per
 // destination per thread -- half the NVLink requests of the 128-bit form for the same bytes.
 // Same rank-order sum and optimizer arithmetic, so results are bit-identical.
-template <int N, int OPT>
+template <int N, int OPT, int U>
 __global__ void __launch_bounds__(kStepThreads)
 step256_kernel(const StepArgs a) {
   const bool ok = flag_barrier(a.c, 0);
   const int64_t nvec8 = ok ? (a.nvec >> 1) : 0;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float sumsq = 0.0f, bad = 0.0f;
-  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec8; q += stride) {
-    float8 g[N];
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < nvec8; base += stride * U) {
+    float8 g[U][N];
+    float8 w[U], s0[U], s1[U];
 #pragma unroll
-    for (int r = 0; r < N; ++r) g[r] = ld_stream_f8(reinterpret_cast<const float*>(a.g[r]) + q * 8);
-    float8 w, s0, s1;
-    if (OPT != B2DP_OPT_NONE) {
-      w = ld_stream_f8(a.w + q * 8);
-      s0 = ld_stream_f8(a.s0 + q * 8);
-      if (OPT == B2DP_OPT_ADAM) s1 = ld_stream_f8(a.s1 + q * 8);
-    }
-    float8 res;
-    float* pr = &res.lo.x;
-    float* pw = &w.lo.x;
-    float* p0 = &s0.lo.x;
-    float* p1 = &s1.lo.x;
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < nvec8) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float acc = (&g[0].lo.x)[i];
-#pragma unroll
-      for (int r = 1; r < N; ++r) acc = __fadd_rn(acc, (&g[r].lo.x)[i]);
-      acc = __fmul_rn(acc, a.o.postscale);
-      if (a.want_stats) {
-        sumsq = fmaf(acc, acc, sumsq);
-        bad += (float)(!isfinite(acc));
-      }
-      if (OPT == B2DP_OPT_ADAM) {
-        adam_update(acc, pw[i], p0[i], p1[i], a.o);
-        pr[i] = pw[i];
-      } else if (OPT == B2DP_OPT_SGDM) {
-        sgdm_update(acc, pw[i], p0[i], a.o);
-        pr[i] = pw[i];
-      } else {
-        pr[i] = acc;
+        for (int r = 0; r < N; ++r) g[u][r] = ld_stream_f8(reinterpret_cast<const float*>(a.g[r]) + q * 8);
+        if (OPT != B2DP_OPT_NONE) {
+          w[u] = ld_stream_f8(a.w + q * 8);
+          s0[u] = ld_stream_f8(a.s0 + q * 8);
+          if (OPT == B2DP_OPT_ADAM) s1[u] = ld_stream_f8(a.s1 + q * 8);
+        }
       }
     }
-    if (OPT == B2DP_OPT_ADAM) {
-      st_f8(a.s0 + q * 8, s0);
-      st_f8(a.s1 + q * 8, s1);
-    } else if (OPT == B2DP_OPT_SGDM && a.o.mu != 0.0f) {
-      st_f8(a.s0 + q * 8, s0);
-    }
-    if (N > 1 && a.push) {
 #pragma unroll
-      for (int r = 0; r < N; ++r) st_f8(a.out[r] + q * 8, res);
-    } else {
-      st_f8(a.w + q * 8, res);
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = base + u * stride;
+      if (q < nvec8) {
+        float8 res;
+        float* pr = &res.lo.x;
+        float* pw = &w[u].lo.x;
+        float* p0 = &s0[u].lo.x;
+        float* p1 = &s1[u].lo.x;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float acc = (&g[u][0].lo.x)[i];
+#pragma unroll
+          for (int r = 1; r < N; ++r) acc = __fadd_rn(acc, (&g[u][r].lo.x)[i]);
+          acc = __fmul_rn(acc, a.o.postscale);
+          if (a.want_stats) {
+            sumsq = fmaf(acc, acc, sumsq);
+            bad += (float)(!isfinite(acc));
+          }
+          if (OPT == B2DP_OPT_ADAM) {
+            adam_update(acc, pw[i], p0[i], p1[i], a.o);
+            pr[i] = pw[i];
+          } else if (OPT == B2DP_OPT_SGDM) {
+            sgdm_update(acc, pw[i], p0[i], a.o);
+            pr[i] = pw[i];
+          } else {
+            pr[i] = acc;
+          }
+        }
+        if (OPT == B2DP_OPT_ADAM) {
+          st_f8(a.s0 + q * 8, s0[u]);
+          st_f8(a.s1 + q * 8, s1[u]);
+        } else if (OPT == B2DP_OPT_SGDM && a.o.mu != 0.0f) {
+          st_f8(a.s0 + q * 8, s0[u]);
+        }
+        if (N > 1 && a.push) {
+#pragma unroll
+          for (int r = 0; r < N; ++r) st_f8(a.out[r] + q * 8, res);
+        } else {
+          st_f8(a.w + q * 8, res);
+        }
+      }
     }
   }
   if (a.want_stats) stats_reduce(a, (double)sumsq, (double)bad);

@@ -633,3 +633,31 @@ def test_stats_cover_every_bucket_of_the_call(n, call):
             want = oracle.sumsq(gsum)
             assert abs(stats[:, 0].sum() - want) <= 1e-6 * want, (stats, want)   # tolerance: rel 1e-6
             assert stats[:, 1].sum() == 0
+
+
+def test_more_tensors_than_fit_in_launch_parameters():
+    """Up to 448 tensor pointers ride in the resolve kernel's launch parameters; a longer list goes
+    through a device-resident pointer table.  600 tensors: pack -> fused step -> unpack vs the
+    oracle, then the same with every gradient at a NEW address (the table must be re-resolved)."""
+    rng = np.random.default_rng(21)
+    numels = [int(x) for x in rng.integers(1, 300, 600)]
+    N = sum(numels)
+    for n in (1, 2):
+        ctx, lay, plan = make_plan(numels, n)
+        w0 = (rng.standard_normal(N) * 0.05).astype(F)
+        for r in range(n):
+            plan.load_weights(r, dev(split(w0, numels)))
+        w, m, v = w0.copy(), np.zeros(N, F), np.zeros(N, F)
+        for step in (1, 2):
+            hg = [(rng.standard_normal(N) * 1e-2).astype(F) for _ in range(n)]
+            gts = [dev(split(g, numels)) for g in hg]          # fresh tensors: new addresses every step
+            if n == 1:
+                plan.pack_step(0, gts[0], "adam", b200dp.adam_hyper(step=step))
+            else:
+                for r in range(n):
+                    plan.pack(r, gts[r])
+                for r in range(n):
+                    plan.step(r, "adam", b200dp.adam_hyper(step=step))
+            oracle.adam_(w, m, v, oracle.addn(hg), step=step)
+        for r in range(n):
+            assert np.array_equal(bits(read_tensors(plan, r, numels)), bits(w)), "n=%d rank %d" % (n, r)
