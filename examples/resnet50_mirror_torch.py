@@ -49,9 +49,10 @@ def main():
         for r in devices:                                      # replicas run concurrently: launches are async
             with torch.cuda.device(r):
                 losses.append(steppers[r].forward_backward(*data[r]))
-        for r in devices:                                      # one collective call per replica, same order
-            with torch.cuda.device(r):
-                steppers[r].hot_path()
+        with b200dp.issue_group():                             # nothing may block the host between the replicas' calls
+            for r in devices:                                  # one collective call per replica, same order
+                with torch.cuda.device(r):
+                    steppers[r].hot_path()
         for r in devices:
             torch.cuda.synchronize(r)
         print("step %d  loss %.4f  %.1f images/s" % (step + 1, sum(float(l) for l in losses),

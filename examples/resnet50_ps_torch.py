@@ -59,12 +59,13 @@ def main():
         for r in devices:                                      # workers hand their gradients over
             with torch.cuda.device(r):
                 plan.pack(r, [p.grad for p in steppers[r].params])
-        for r in devices:                                      # PUSH: reduce on the slice owner + apply there
-            with torch.cuda.device(r):
-                plan.reduce_scatter_apply(r, "adam", h)
-        for r in devices:                                      # PULL: every replica fetches the fresh slices
-            with torch.cuda.device(r):
-                plan.all_gather(r)
+        with b200dp.issue_group():
+            for r in devices:                                  # PUSH: reduce on the slice owner + apply there
+                with torch.cuda.device(r):
+                    plan.reduce_scatter_apply(r, "adam", h)
+            for r in devices:                                  # PULL: every replica fetches the fresh slices
+                with torch.cuda.device(r):
+                    plan.all_gather(r)
         for r in devices:
             torch.cuda.synchronize(r)
         print("step %d  loss %.4f" % (step, sum(float(l) for l in losses)))

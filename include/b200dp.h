@@ -33,6 +33,13 @@
  *     stream (or serialised with events).  Two collectives of the same plan in flight on
  *     different streams can satisfy each other's waits and read buckets that are not packed
  *     yet.  Use separate plans for traffic that must overlap (e.g. metrics on a side stream).
+ *   - a local context driven by ONE host thread: between the first and the last rank's call of a
+ *     collective the host must not block on any of the devices (cudaFree, cudaDeviceSynchronize, a
+ *     synchronous memcpy, b2dp_plan_destroy of another plan): the kernels already launched wait on
+ *     the GPU for the ranks still to be launched.  This is what ncclGroupStart/End is for in NCCL;
+ *     here the calls themselves never block, so it is enough not to put anything blocking between
+ *     them (Python: `with b200dp.issue_group():`, which also keeps the garbage collector from
+ *     running a destructor there).  One host thread per device has no such constraint.
  *   - if a cross-GPU flag wait gives up (a peer never reached the collective within the
  *     context's timeout), the waiting blocks leave their slice untouched, the rank's status
  *     word is set, and every later collective call of that rank returns B2DP_ERR_TIMEOUT
@@ -166,9 +173,10 @@ int b2dp_plan_check(b2dp_plan* p, int32_t dev, void* stream);
  * order (parity within (n-1)*2^-24*sum|g_i|, not bitwise) -- the same trade NCCL's NVLS
  * all-reduce makes under MultiWorkerMirroredStrategy(NCCL) (-multiworkers.py:20-21).
  * With a bf16 wire the switch accumulates the n bf16 copies in fp32 and returns the sum
- * rounded ONCE more to bf16 (multimem.ld_reduce .acc::f32 .bf16x2): within
- * 2^-8*|sum| + (n-1)*2^-24*sum|b_i| of the bf16-wire oracle (b_i = RNE bf16 of g_i) and
- * 2^-7*sum|g_i| of the fp32 oracle; the weights still travel as fp32.  Local context: multicast_create does everything (fd_out = -1).
+ * converted ONCE more to bf16 (multimem.ld_reduce .acc::f32 .bf16x2; the rounding of that
+ * conversion is not documented, so one bf16 ulp is allowed): within
+ * 2^-7*|sum| + (n-1)*2^-24*sum|b_i| of the bf16-wire oracle (b_i = RNE bf16 of g_i) and
+ * 3*2^-8*sum|g_i| of the fp32 oracle; the weights still travel as fp32.  Local context: multicast_create does everything (fd_out = -1).
  * Rank contexts: rank 0 calls multicast_create and ships the fd to every rank; every rank
  * calls multicast_join(fd); after ALL ranks joined, every rank calls multicast_bind; after
  * ALL ranks bound, set_path(B2DP_PATH_MULTICAST). */

@@ -149,6 +149,28 @@ def _stream_handle(stream, device):
     return ctypes.c_void_p(int(stream))
 
 
+class issue_group:
+    """``with b200dp.issue_group():`` around the loop in which ONE host thread issues a collective
+    for every rank of a local context.  Between the first and the last rank's call nothing may block
+    the host on a device -- the kernels already launched wait inside the GPU for the ranks that are
+    still to be launched (the reason NCCL has ncclGroupStart/End).  The calls of this library never
+    block; what can is Python's garbage collector running some object's destructor at an arbitrary
+    point (an old Plan's destroy synchronises its devices; torch frees memory): the context manager
+    keeps the cyclic collector off for the duration of the loop."""
+
+    def __enter__(self):
+        import gc
+        self._was = gc.isenabled()
+        gc.disable()
+        return self
+
+    def __exit__(self, *exc):
+        import gc
+        if self._was:
+            gc.enable()
+        return False
+
+
 def ptr_array(tensors_or_ptrs):
     """ctypes array of device pointers; build it once and reuse it when the tensors' addresses
     are stable (214 data_ptr() calls cost more host time than the pack kernel takes)."""

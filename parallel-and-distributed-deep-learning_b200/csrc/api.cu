@@ -278,7 +278,9 @@ struct Tuning {
 
 template <int N, int OPT>
 int launch_step256(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
-  if (t.unroll == 2 && N == 2) {   // two 256-bit vectors per peer in flight per thread (tuning knob; spills for N >= 4)
+  // N == 2: two 256-bit vectors per peer in flight per thread unless the caller asked for one
+  // (r02 sweep on 2 x B200: 171.7 vs 175.6 us; with N >= 4 the second vector spills registers)
+  if ((t.unroll == 2 || t.unroll == 0) && N == 2) {
     auto kernel = step256_kernel<N, OPT, (N == 2 ? 2 : 1)>;
     const int grid = step_grid(kernel, r, a.nvec >> 1, 2, t.grid_cap);
     kernel<<<grid, kStepThreads, 0, s>>>(a);

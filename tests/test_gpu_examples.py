@@ -13,6 +13,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NGPU = torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
+def free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return str(port)
+
+
 def run(cmd, timeout=600):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
     assert out.returncode == 0, (out.stdout[-1500:], out.stderr[-3000:])
@@ -33,7 +42,7 @@ def test_mirror_example_all_gpus():
 @pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
 def test_hvd_example_two_ranks_torchrun():
     out = run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-               "127.0.0.1", "--master-port", "29577", "examples/resnet50_hvd_torch.py", "--steps", "2", "--batch", "4"])
+               "127.0.0.1", "--master-port", free_port(), "examples/resnet50_hvd_torch.py", "--steps", "2", "--batch", "4"])
     assert "mean loss over 2 ranks" in out and "All done for rank 1" in out
 
 
@@ -55,7 +64,7 @@ def test_ps_example_single_gpu_saves_a_partitioned_checkpoint(tmp_path):
 @pytest.mark.parametrize("fused", [False, True])
 def test_multiworkers_example_two_workers(fused):
     out = run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-               "127.0.0.1", "--master-port", "29578", "examples/resnet50_multiworkers_torch.py", "--steps", "2",
+               "127.0.0.1", "--master-port", free_port(), "examples/resnet50_multiworkers_torch.py", "--steps", "2",
                "--batch", "4"] + (["--fused"] if fused else []))
     assert "worker 1 holds the same weights as worker 0: True" in out and "All done for worker 1" in out
 

@@ -67,9 +67,10 @@ def test_local_context_distinct_gpus_bit_exact(wire):
         for r in range(n):
             with torch.cuda.device(r):
                 plan.pack(r, views(dg[r], numels))
-        for r in range(n):          # all ranks' kernels are in flight together; each waits for its peers
-            with torch.cuda.device(r):
-                plan.step(r, "adam", b200dp.adam_hyper(step=s + 1))
+        with b200dp.issue_group():
+            for r in range(n):      # all ranks' kernels are in flight together; each waits for its peers
+                with torch.cuda.device(r):
+                    plan.step(r, "adam", b200dp.adam_hyper(step=s + 1))
         for r in range(n):
             torch.cuda.synchronize(r)
         oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(hg, bf16_wire=(wire == "bf16")), step=s + 1)
@@ -207,8 +208,18 @@ def _path_b_checks(plan, lay, n, numels, local_devs, ops, sync, wire="f32"):
     if wire == "bf16":
         # the switch adds the bf16 copies in fp32 and rounds the sum once more to bf16
         ref32 = oracle.addn(hg, bf16_wire=True)
-        bound = bounds.sum_bound_bf16_switch([oracle_np.bf16_round(g) for g in hg], ref32)
-        bound_vs_fp32 = 2.0 ** -7 * np.sum(np.abs(np.stack(hg)), axis=0) + 1e-30
+        rb = [oracle_np.bf16_round(g) for g in hg]
+        bound = bounds.sum_bound_bf16_switch(rb, ref32)
+        if os.environ.get("B2DP_REPORT_SWITCH_ROUNDING"):       # how the switch rounds its fp32 sum to bf16, measured
+            for dev in local_devs:
+                got = _flat(plan, lay, numels, b200dp.BUF_REDUCED, dev).astype(np.float64)
+                nz = np.abs(ref32) > 0
+                rel = np.abs(got - ref32)[nz] / np.abs(ref32[nz].astype(np.float64))
+                print("SWITCH_BF16_ROUNDING n=%d max_rel_err=%.6g (2^-8=%.6g 2^-7=%.6g) frac_over_2^-8=%.3g frac_on_bf16_grid=%.4f"
+                      % (n, rel.max(), 2.0 ** -8, 2.0 ** -7, float((rel > 2.0 ** -8 * 1.0001).mean()),
+                         float(np.mean(oracle_np.bf16_round(got.astype(F)) == got.astype(F)))), flush=True)
+        # vs the fp32 oracle: every g_i moves by <= 2^-8|g_i| when cast, the switch's result by <= 2^-7|sum|
+        bound_vs_fp32 = 3 * 2.0 ** -8 * np.sum(np.abs(np.stack(hg)), axis=0) + 1e-30
         ref_fp32 = oracle.addn(hg).astype(np.float64)
     else:
         ref32 = oracle.addn(hg)
@@ -218,7 +229,7 @@ def _path_b_checks(plan, lay, n, numels, local_devs, ops, sync, wire="f32"):
         got = _flat(plan, lay, numels, b200dp.BUF_REDUCED, dev).astype(np.float64)
         assert np.all(np.abs(got - ref) <= bound), "all-reduce outside the order-free bound"
         if wire == "bf16":
-            assert np.all(np.abs(got - ref_fp32) <= bound_vs_fp32), "bf16 gradient mode outside 2^-7 * sum|g_i| of the fp32 oracle"
+            assert np.all(np.abs(got - ref_fp32) <= bound_vs_fp32), "bf16 gradient mode outside 3 * 2^-8 * sum|g_i| of the fp32 oracle"
     # (2) fused SGD step on the same data: linear error bound
     w0 = ((torch.rand(N, generator=torch.Generator().manual_seed(42)) - 0.5) * 0.1).numpy()
     ops.load(w0)
@@ -248,7 +259,10 @@ def _path_b_checks(plan, lay, n, numels, local_devs, ops, sync, wire="f32"):
         res = parity.run(plan, ops.locals, dist_name=dist_name)
         assert res["ok"], res
         assert res["violations"] == 0 and res["max_err_over_bound"] <= 1.0
-        assert res["w_median_bound"] <= 1e-7, res      # the bound says something: a few ulp of |w|
+        if wire == "f32":
+            assert res["w_median_bound"] <= 1e-7, res  # the bound says something: a few ulp of |w|
+        else:                                          # a bf16 wire moves the gradient by up to 2^-7 of itself
+            assert res["w_median_bound"] <= 1e-4, res
 
 
 class _Ops:
@@ -267,9 +281,10 @@ def test_path_b_multicast_local_context(wire):
     plan.enable_multicast()
 
     def each(fn):
-        for r in range(n):
-            with torch.cuda.device(r):
-                fn(r)
+        with b200dp.issue_group():
+            for r in range(n):
+                with torch.cuda.device(r):
+                    fn(r)
 
     ops = _Ops()
     ops.put = lambda hg: each(lambda r: plan.pack(r, views(torch.from_numpy(hg[r]).cuda(r), numels)))

@@ -80,26 +80,33 @@ def test_300_steps_with_random_rank_skew(path, bucket_bytes):
         delay = int(rng.integers(0, 4_000_000))
         h = b200dp.adam_hyper(lr=1e-3, step=step)
         order = list(rng.permutation(n))                  # and the host issues the ranks in a random order
-        for r in order:
-            with torch.cuda.device(int(r)):
-                if r == slow:
-                    torch.cuda._sleep(delay)
-                plan.pack_step(int(r), views(dg[r], NUMELS), "adam", h)
+        with b200dp.issue_group():                        # nothing may block the host between the ranks' launches
+            for r in order:
+                with torch.cuda.device(int(r)):
+                    if r == slow:
+                        torch.cuda._sleep(delay)
+                    try:
+                        plan.pack_step(int(r), views(dg[r], NUMELS), "adam", h)
+                    except b200dp.B200dpError as e:
+                        raise AssertionError("step %d, rank %d (issue order %s, slow rank %d): %s" % (step, r, order, slow, e))
         oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(hg), lr=1e-3, step=step)
         if step % 10 == 0:                                # metric averaging between steps
             vals = [np.array([r + step, -r, 0.5 * r, step, 1.0], F) for r in range(n)]
-            for r in order:
-                with torch.cuda.device(int(r)):
-                    small_in[r].copy_(torch.from_numpy(vals[r]))
-                    plan.allreduce_small(int(r), small_in[r], small_out[r], postscale=1.0 / n)
+            for r in range(n):
+                small_in[r].copy_(torch.from_numpy(vals[r]))      # a blocking copy: before the group, not inside it
+            with b200dp.issue_group():
+                for r in order:
+                    with torch.cuda.device(int(r)):
+                        plan.allreduce_small(int(r), small_in[r], small_out[r], postscale=1.0 / n)
             want = oracle.scale(oracle.addn(vals), 1.0 / n)
             for r in range(n):
                 assert np.array_equal(bits(small_out[r].cpu().numpy()), bits(want)), "small all-reduce, step %d rank %d" % (step, r)
         if step % 50 == 0:                                # a re-broadcast of the (identical) weights from a rotating root
             root = (step // 50) % n
-            for r in order:
-                with torch.cuda.device(int(r)):
-                    plan.broadcast(int(r), root=root)
+            with b200dp.issue_group():
+                for r in order:
+                    with torch.cuda.device(int(r)):
+                        plan.broadcast(int(r), root=root)
         if step % 25 == 0:
             r = (step // 25) % n
             torch.cuda.synchronize(r)

@@ -32,26 +32,26 @@ def main():
                     plan.enable_multicast()
                 except b200dp.B200dpError:
                     have_mc = False
-                grads = []
+                grads, keep = [], []
                 for r in range(n):
                     with torch.cuda.device(r):
                         g = torch.randn(sum(numels), device="cuda:%d" % r) * 1e-3
+                        keep.append(g)
                         grads.append(b200dp.ptr_array(views(g, numels)))
                         plan.pack(r, grads[r])
                         plan.tensor(r, b200dp.BUF_WEIGHTS).uniform_(-0.05, 0.05)
-                    grads.append(g)   # keep alive
                 t = [0]
 
                 def call(r):
                     if r == 0:
                         t[0] += 1
-                    plan.pack_step(r, grads[2 * r], "adam", b200dp.adam_hyper(step=t[0] + 1))
+                    plan.pack_step(r, grads[r], "adam", b200dp.adam_hyper(step=t[0] + 1))
 
                 def step(r):
                     plan.step(r, "adam", b200dp.adam_hyper(step=t[0] + 1))
 
                 def pack(r):
-                    plan.pack(r, grads[2 * r])
+                    plan.pack(r, grads[r])
 
                 configs = []
                 if wire == "f32":
@@ -80,7 +80,7 @@ def main():
                                       "call_us": round(us_call, 1), "step_us": round(us_step, 1), "pack_us": round(us_pack, 1),
                                       "call_minus_step_us": round(us_call - us_step, 1),
                                       "step_busbw": round(S / us_step * 2 * (n - 1) / n / 1e3, 1)}), flush=True)
-                del plan, ctx, grads
+                del plan, ctx, grads, keep
 
 
 if __name__ == "__main__":
