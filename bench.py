@@ -637,8 +637,9 @@ def run_b200dp(args):
             nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S
         achieved = nvl_bytes / (step_avg_ms * 1e-3) / 1e9
         roofline = {"kernel": ("step_mc_kernel<%s> (multimem.ld_reduce + apply + multimem.st through NVSwitch, N=%d)" % (args.optimizer, n)) if plan.path == "multicast" else
-                              "step_kernel<N=%d,%s,%s> (reduce-scatter + apply + all-gather over NVLink peer memory)"
-                              % (n, args.wire, args.optimizer),
+                              ("step256_kernel<N=%d,%s>" % (n, args.optimizer) if (args.wire == "f32" and n in (2, 4, 8))
+                               else "step_kernel<N=%d,%s,%s>" % (n, args.wire, args.optimizer))
+                              + " (reduce-scatter + apply + all-gather over NVLink peer memory)",
                     "bound": "nvlink", "achieved": achieved, "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
                     "frac": achieved / NVLINK_PEAK_GBS,
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
@@ -648,6 +649,17 @@ def run_b200dp(args):
                     "traffic_note": "NVLink data bytes per launch on the busiest GPU and direction (NVML counters); "
                                     "algorithmic_bytes_per_launch is the per-direction payload",
                     "nvlink_counters": nvl_traffic}
+    if n > 1 and plan.path == "peer":
+        # what the same traffic pattern reaches with no arithmetic and no barriers when every GPU issues it at
+        # once (tools/nvlink_ceiling.cu, committed result): the ceiling THIS kernel can be held to
+        try:
+            with open(os.path.join(ROOT, "profiles", "nvlink_ceiling.json")) as f:
+                ceil = json.load(f).get(str(n))
+            if ceil and args.wire == "f32":
+                roofline["measured_pattern_ceiling_gbs"] = ceil["fused_pull_push_gbs_per_direction"]
+                roofline["frac_of_measured_pattern_ceiling"] = achieved / ceil["fused_pull_push_gbs_per_direction"]
+        except Exception:
+            pass
     busbw = (S / (step_avg_ms * 1e-3)) * 2 * (n - 1) / n / 1e9 if n > 1 else 0.0
     hot_path = {"us_per_step_call_median": hot_med_ms * 1e3, "us_per_step_call_after_1s_idle": idle_med_ms * 1e3,
                 "us_per_step_call_new_grad_addresses": refresh_med_ms * 1e3, "us_step_kernel_avg": step_avg_ms * 1e3,
@@ -680,6 +692,11 @@ def run_b200dp(args):
         line["e2e"] = e2e
     if parity_res is not None:
         line["parity"] = parity_res
+    if n > 1:
+        # every other rank leaves now: a rank parked in an NCCL barrier busy-waits on a host core, and one
+        # busy core stalls every OpenMP region of the CPU baseline below (measured: 13x slower)
+        dist.barrier()
+        dist.destroy_process_group()
     if not args.no_cpu_baseline and not args.hotpath_only:
         cpu_steps = 2 if n == 1 else 1
         line["cpu_baseline"] = cpu_baseline_subprocess(n, args.ref_batch, cpu_steps, 1)["cpu_baseline"]
@@ -687,9 +704,6 @@ def run_b200dp(args):
         # against the GPU per-step call (pack + fused reduce-scatter/Adam/all-gather)
         hot_path["hot_path_vs_cpu"] = line["cpu_baseline"]["hot_path_ms"] * 1e3 / hot_path["us_per_step_call_median"]
     print(json.dumps(line))
-    if n > 1:
-        dist.barrier()
-        dist.destroy_process_group()
 
 
 def load_traffic(key):

@@ -1,7 +1,7 @@
 """Round-2 sweep on the GPUs of one box (local context, one process): the per-step call
 (pack_step) with 1 / 2 / 4 buckets (multi-bucket calls pack bucket b+1 under bucket b's step),
 the peer-path geometry (grid cap, 256-bit unroll), and the bf16 wire on both paths.
-Developer tool; prints one JSON line per configuration.  TUNE_N=2,4,8 selects rank counts."""
+Developer tool; prints one JSON line per configuration.  TUNE_N=2,4,8 selects rank counts, TUNE_BUCKETS=1,2,4 the bucket counts (default 1)."""
 import json
 import os
 import sys
@@ -21,7 +21,7 @@ def main():
     numels = b200dp.resnet50_numels()
     for n in [x for x in want if x <= ndev]:
         for wire in ("f32", "bf16"):
-            for nb in (1, 2, 4):
+            for nb in [int(x) for x in os.environ.get("TUNE_BUCKETS", "1").split(",")]:
                 bucket_bytes = 0 if nb == 1 else int(S / nb * (1.02 if wire == "f32" else 0.51))
                 ctx = b200dp.Context.local(list(range(n)))
                 ctx.set_timeout(5.0)
