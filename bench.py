@@ -356,7 +356,7 @@ def run_b200dp(args):
         # auto: the multicast path only pays from 5 ranks up (r01 sweep: n=2 peer 176 vs mc 274 us,
         # n=4 251 vs 247, n=8 294 vs 241); below that the bit-exact peer path is also the faster one
         want_mc = args.path == "multicast" or (args.path == "auto" and n > 4)
-        if want_mc and args.wire == "f32":
+        if want_mc:
             try:
                 plan.enable_multicast(obj[0])
             except b200dp.B200dpError:
@@ -631,12 +631,16 @@ def run_b200dp(args):
                     "traffic": load_traffic("fused_n1" if fused else "step_n1")}
     else:
         wire_b = 2 if args.wire == "bf16" else 4
-        if plan.path == "multicast":   # inbound: S/n reduced + S replicated stores (the switch also writes the
+        if plan.path == "multicast" and args.wire == "bf16":
+            # busier direction = inbound: S replicated fp32 stores + S/(2n) reduced bf16; outbound S/2 + S/n
+            nvl_bytes = S * (1.0 + 0.5 / n)
+        elif plan.path == "multicast":   # inbound: S/n reduced + S replicated stores (the switch also writes the
             nvl_bytes = S * (1.0 + 1.0 / n)   # sender's own copy); outbound the mirror image: S fetched + S/n stored
         else:                          # per GPU per direction: RS reads in + AG writes in
             nvl_bytes = (n - 1) / n * (wire_b * N_ELEMS) + (n - 1) / n * S
         achieved = nvl_bytes / (step_avg_ms * 1e-3) / 1e9
-        roofline = {"kernel": ("step_mc_kernel<%s> (multimem.ld_reduce + apply + multimem.st through NVSwitch, N=%d)" % (args.optimizer, n)) if plan.path == "multicast" else
+        roofline = {"kernel": ("%s<%s> (multimem.ld_reduce + apply + multimem.st through NVSwitch, N=%d)"
+                               % ("step_mc_bf16_kernel" if args.wire == "bf16" else "step_mc_kernel", args.optimizer, n)) if plan.path == "multicast" else
                               ("step256_kernel<N=%d,%s>" % (n, args.optimizer) if (args.wire == "f32" and n in (2, 4, 8))
                                else "step_kernel<N=%d,%s,%s>" % (n, args.wire, args.optimizer))
                               + " (reduce-scatter + apply + all-gather over NVLink peer memory)",
