@@ -4,7 +4,7 @@ The peer path adds the n gradient copies in rank order and is compared with the 
 bit.  The NVSwitch multicast path (and NCCL) add them in an order of their own, so the reduced
 gradient g^ is only known to satisfy |g^ - g| <= B elementwise, with
 
-    f32 wire:   B = (n-1) * 2^-24 * sum_i |g_i|
+    f32 wire:   B = (n-1) * 2^-24 * sum_i |g_i| + |oracle_sum - exact_sum|   (see sum_bound_f32)
     bf16 wire:  B = 2^-7 * |sum_i b_i| + (n-1) * 2^-24 * sum_i |b_i|     (b_i = RNE bf16 of g_i;
                 the switch accumulates in fp32 and converts the sum once more to bf16 -- one
                 bf16 ulp, since the rounding mode of that conversion is not documented)
@@ -36,18 +36,29 @@ SWITCH_BF16_ULPS = 2.0
 CHUNK = 1 << 22
 
 
-def sum_bound_f32(grads, n=None):
-    """(n-1) * 2^-24 * sum_i |g_i|, elementwise, float64."""
-    n = len(grads) if n is None else n
+def sum_bound_f32(grads, oracle_sum=None):
+    """Bound on |s^ - oracle_sum| for s^ = the n values added in fp32 in ANY order.
+
+    SURVEY 8c's (n-1) * 2^-24 * sum_i |g_i| bounds ONE fp32 summation against the EXACT sum.  The
+    oracle's rank-order sum is itself such a summation, so two orders may differ by the sum of
+    their two errors (measured: NCCL at n = 4 sits 1.33x the one-sided figure away from AddN on D1
+    data).  The oracle's own error is not bounded but COMPUTED -- the float64 sum of <= 8 fp32
+    values is exact to 2^-53 -- and added: B = (n-1) 2^-24 sum|g_i| + |oracle - exact|."""
+    n = len(grads)
     acc = np.zeros(grads[0].size, np.float64)
+    exact = np.zeros(grads[0].size, np.float64)
     for g in grads:
         acc += np.abs(g, dtype=np.float64)
-    return (n - 1) * U32 * acc + 1e-38
+        exact += g
+    B = (n - 1) * U32 * (1 + 1e-6) * acc + 1e-38
+    if oracle_sum is not None:
+        B += np.abs(np.asarray(oracle_sum, np.float64) - exact)
+    return B
 
 
 def sum_bound_bf16_switch(bgrads, bsum):
-    """bgrads: the bf16-rounded gradients (as fp32 arrays); bsum: their oracle sum (fp32)."""
-    return SWITCH_BF16_ULPS * 2.0 ** -8 * np.abs(bsum, dtype=np.float64) + sum_bound_f32(bgrads)
+    """bgrads: the bf16-rounded gradients (as fp32 arrays); bsum: their oracle (rank-order fp32) sum."""
+    return SWITCH_BF16_ULPS * 2.0 ** -8 * np.abs(bsum, dtype=np.float64) + sum_bound_f32(bgrads, bsum)
 
 
 class AdamBound:

@@ -84,8 +84,9 @@ def run(plan, locals_, dist_name="D1", average=False, nccl=False, threads=None, 
             import torch.distributed as tdist
             t = dg[locals_[0][1]].clone()
             tdist.all_reduce(t)
-            ref = addn(hg).astype(np.float64)
-            B = bounds.sum_bound_f32(hg)
+            ref32 = addn(hg)
+            ref = ref32.astype(np.float64)
+            B = bounds.sum_bound_f32(hg, ref32)
             ratio = np.abs(t.cpu().numpy().astype(np.float64) - ref) / B
             nccl_ok, nccl_ratio = bool(np.all(ratio <= 1.0)), float(ratio.max())
         gsum = addn(hg, bf16_wire=wire_bf16)
@@ -94,7 +95,7 @@ def run(plan, locals_, dist_name="D1", average=False, nccl=False, threads=None, 
                 from .oracle_np import bf16_round
                 B = bounds.sum_bound_bf16_switch([bf16_round(g) for g in hg], gsum)
             else:
-                B = bounds.sum_bound_f32(hg)
+                B = bounds.sum_bound_f32(hg, gsum)
             B = B * post
         if average:
             scale(gsum, post)

@@ -195,7 +195,7 @@ def test_interval_bound_holds_for_any_summation_order(dist, order):
         else:
             a = [(hg[2 * i] + hg[2 * i + 1]).astype(F) for i in range(4)]
             gh = ((a[0] + a[1]).astype(F) + (a[2] + a[3]).astype(F)).astype(F)
-        B = bounds.sum_bound_f32(hg)
+        B = bounds.sum_bound_f32(hg, gs)
         assert np.all(np.abs(gh.astype(np.float64) - gs) <= B)
         mo, vo = m.copy(), v.copy()
         oracle.adam_(w, m, v, gs, lr=lr, step=s + 1)
