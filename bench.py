@@ -218,6 +218,11 @@ def run_reference(args):
         print(json.dumps(line))
         return
     steps, warmup = max(1, args.steps), max(1, args.warmup)
+    # the same `config` as the GPU arm of this N (what the CPU arm samples of it is in cpu_baseline.sample)
+    if args.gpus == 1:
+        args.path_used = "n/a (single GPU)"
+    else:
+        args.path_used = args.path if args.path != "auto" else ("multicast" if args.gpus > 4 else "peer")
     r = cpu_training_step_baseline(args.gpus, args.ref_batch, steps, warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["images_per_s"], "unit": UNIT, "n_gpus": args.gpus,
