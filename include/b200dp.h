@@ -194,7 +194,9 @@ typedef enum {
   B2DP_TUNE_MC_UNROLL = 2,   /* multicast path: vectors in flight per thread (1, 2, 4) */
   B2DP_TUNE_PEER_UNROLL = 3, /* peer path: 0 = automatic, 1 or 2 */
   B2DP_TUNE_PEER_VEC = 4,    /* peer path, f32 wire, n in {2,4,8}: 4 = 128-bit or 8 = 256-bit accesses */
-  B2DP_TUNE_MC_BF16_GRID_CAP = 5 /* multicast path, bf16 wire: max blocks */
+  B2DP_TUNE_MC_BF16_GRID_CAP = 5, /* multicast path, bf16 wire: max blocks */
+  B2DP_TUNE_SKIP_OWN = 6     /* pack_step, peer path, f32 wire: 1 = the rank's own slice is not packed but read in
+                                place by the step kernel (bit-identical; measured no faster); 0 (default) = pack everything */
 } b2dp_tune;
 int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value);
 
@@ -227,7 +229,11 @@ int b2dp_step(b2dp_plan* p, int32_t dev, int32_t bucket, int32_t opt, const b2dp
  * one rank and an f32 wire (imagenet-resnet50.py:62,67: no reduction, 214 x ResourceApplyAdam)
  * it is a single kernel that reads each gradient in place through the tile table and never
  * materialises the bucket (28 instead of 36 bytes of HBM traffic per element); with n > 1 it
- * is b2dp_pack followed by b2dp_step.  Results are bit-identical to the two-call form. */
+ * is b2dp_pack followed by b2dp_step -- except that with several buckets bucket b+1 is packed on an
+ * internal stream under bucket b's step, and that with B2DP_TUNE_SKIP_OWN (peer path, f32 wire,
+ * 2/4/8 ranks) the rank's own slice of each bucket is left unpacked and read in place by the step
+ * kernel.  The gradient tensors must stay untouched until the call's work has run.
+ * Results are bit-identical to the two-call form. */
 int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const void* const* grads,
                    int32_t grad_dtype, float prescale, int32_t opt, const b2dp_hyper* hyper,
                    void* stream);

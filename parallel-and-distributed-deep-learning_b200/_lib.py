@@ -14,7 +14,7 @@ OPT_NONE, OPT_ADAM, OPT_SGDM = 0, 1, 2
 BUF_GRADS, BUF_WEIGHTS, BUF_REDUCED, BUF_STATE0, BUF_STATE1, BUF_STATS = range(6)
 NOALLOC_MAX_ELEMS = 1 << 26
 PATH_PEER, PATH_MULTICAST = 0, 1
-TUNE = {"grid_cap": 0, "mc_grid_cap": 1, "mc_unroll": 2, "peer_unroll": 3, "peer_vec": 4, "mc_bf16_grid_cap": 5}
+TUNE = {"grid_cap": 0, "mc_grid_cap": 1, "mc_unroll": 2, "peer_unroll": 3, "peer_vec": 4, "mc_bf16_grid_cap": 5, "skip_own": 6}
 
 
 class Hyper(ctypes.Structure):

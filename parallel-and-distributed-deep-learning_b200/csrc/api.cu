@@ -147,6 +147,8 @@ struct b2dp_plan {
   int mc_grid_cap = 74;       // multicast path: fewer blocks contend less in the switch
   int mc_unroll = 1;
   int mc_bf16_grid_cap = 148; // multicast path, bf16 wire (8 elements per request)
+  int skip_own = 0;           // pack_step, peer path: leave the rank's own slice unpacked and read it in place
+                              // (opt-in: measured no faster)
   int peer_unroll = 0;        // 0 = automatic (1 for n == 8, else 2)
   int peer_vec = 8;           // elements per peer access: 8 (256-bit; f32 wire, n in {2,4,8}) or 4 (128-bit)
 };
@@ -228,7 +230,7 @@ int pack_grid(const RankState&, int64_t ntiles) { return (int)ntiles; }  // one 
 
 template <int DIR>
 int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const void* const* ptrs,
-                size_t flat_off, int wire, float prescale, cudaStream_t s) {
+                size_t flat_off, int wire, float prescale, cudaStream_t s, int64_t skip_lo = 0, int64_t skip_hi = 0) {
   int b0 = 0, b1 = 0;
   if (int rc = bucket_range(p, bucket, &b0, &b1)) return rc;
   if (!ptrs && p->layout.K > 0) return fail(B2DP_ERR_INVALID, "tensor pointer array is null");
@@ -247,17 +249,18 @@ int launch_pack(b2dp_plan* p, RankState& r, int bucket, PtrTable& table, const v
   char* flat = r.base[r.rank] + flat_off;
   const int grid = pack_grid(r, nt);
   if (wire == B2DP_F32)
-    pack_kernel<float, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (float*)flat, prescale);
+    pack_kernel<float, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (float*)flat, prescale, skip_lo, skip_hi);
   else
-    pack_kernel<__nv_bfloat16, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (__nv_bfloat16*)flat, prescale);
+    pack_kernel<__nv_bfloat16, DIR><<<grid, kPackThreads, 0, s>>>(table.abs + t0, nt, (__nv_bfloat16*)flat, prescale,
+                                                                  skip_lo, skip_hi);
   CUDA_TRY(cudaGetLastError());
   return B2DP_OK;
 }
 
 template <typename KernelT>
-int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_cap = kMaxBlocks) {
+int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_cap = kMaxBlocks, size_t dyn_smem = 0) {
   int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kStepThreads, 0) != cudaSuccess || occ < 1) {
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kStepThreads, dyn_smem) != cudaSuccess || occ < 1) {
     (void)cudaGetLastError();
     occ = 1;
   }
@@ -274,23 +277,28 @@ int step_grid(KernelT kernel, const RankState& r, int64_t nvec, int U, int grid_
 
 struct Tuning {
   int grid_cap, unroll, vec = 4;
+  bool own = false;   // the rank's own slice is read in place from the gradient tensors (a.own_* set)
 };
 
 template <int N, int OPT>
 int launch_step256(const RankState& r, const StepArgs& a, const Tuning& t, cudaStream_t s) {
   // N == 2: two 256-bit vectors per peer in flight per thread unless the caller asked for one
   // (r02 sweep on 2 x B200: 171.7 vs 175.6 us; with N >= 4 the second vector spills registers)
-  if ((t.unroll == 2 || t.unroll == 0) && N == 2) {
-    auto kernel = step256_kernel<N, OPT, (N == 2 ? 2 : 1)>;
-    const int grid = step_grid(kernel, r, a.nvec >> 1, 2, t.grid_cap);
-    kernel<<<grid, kStepThreads, 0, s>>>(a);
-    CUDA_TRY(cudaGetLastError());
-    return B2DP_OK;
-  }
-  auto kernel = step256_kernel<N, OPT, 1>;
-  const int grid = step_grid(kernel, r, a.nvec >> 1, 1, t.grid_cap);
-  kernel<<<grid, kStepThreads, 0, s>>>(a);
-  CUDA_TRY(cudaGetLastError());
+  const size_t smem = t.own ? (size_t)a.own_ntiles * kOwnTileBytes + 16 : 0;   // the bucket's tile table (own slice read in place)
+  auto go = [&](auto kernel, int U) {
+    const int grid = step_grid(kernel, r, a.nvec >> 1, U, t.grid_cap, smem);
+    kernel<<<grid, kStepThreads, smem, s>>>(a);
+    return cudaGetLastError();
+  };
+  cudaError_t e;
+  constexpr int U2 = (N == 2 ? 2 : 1);
+  const bool two = (t.unroll == 2 || t.unroll == 0) && N == 2;
+  if (t.own && OPT != B2DP_OPT_NONE)
+    e = two ? go(step256_kernel<N, (OPT == B2DP_OPT_NONE ? B2DP_OPT_ADAM : OPT), U2, true>, U2)
+            : go(step256_kernel<N, (OPT == B2DP_OPT_NONE ? B2DP_OPT_ADAM : OPT), 1, true>, 1);
+  else
+    e = two ? go(step256_kernel<N, OPT, U2, false>, U2) : go(step256_kernel<N, OPT, 1, false>, 1);
+  if (e != cudaSuccess) return fail(B2DP_ERR_CUDA, "step launch: %s", cudaGetErrorString(e));
   return B2DP_OK;
 }
 
@@ -442,7 +450,7 @@ int fill_opt(int opt, const b2dp_hyper* h, float postscale, OptScalars* o) {
 
 // mode 0: fused step (push), 1: reduce-scatter + apply only, 2: all-reduce, 3: all-gather only
 int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper* h, float postscale, int mode,
-                   void* stream, bool stats_continue = false) {
+                   void* stream, bool stats_continue = false, const float* own_prescale = nullptr) {
   Range nvtx_range("b2dp::collective");
   RankState* rp = nullptr;
   if (int rc = get_rank(p, dev, &rp)) return rc;
@@ -482,6 +490,15 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     stats_started = true;
     a.push = (mode == 1) ? 0 : 1;
     fill_comm(p, r, &a.c);
+    Tuning peer_tune{p->grid_cap, p->peer_unroll, p->peer_vec};
+    if (own_prescale && bk.tile_count <= kOwnMaxTiles) {   // b2dp_pack_step left this rank's own slice unpacked: the kernel reads it in place
+      a.own_tiles = r.grads.abs + bk.tile_first;
+      a.own_ntiles = (int32_t)bk.tile_count;
+      a.own_bucket_off = bk.offset;
+      a.own_rel8 = ((int64_t)r.rank * bk.slice) >> 3;
+      a.prescale = *own_prescale;
+      peer_tune.own = true;
+    }
     int rc;
     if (n == 1 && p->layout.wire == B2DP_F32 && opt != B2DP_OPT_NONE && mode != 3) {
       const int64_t nvec8 = a.nvec >> 1;
@@ -513,11 +530,11 @@ int run_collective(b2dp_plan* p, int dev, int bucket, int opt, const b2dp_hyper*
     } else if (mode == 3)
       rc = launch_gather(n, r, a, s);
     else if (opt == B2DP_OPT_ADAM)
-      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
+      rc = launch_step_o<B2DP_OPT_ADAM>(p->layout.wire, n, r, a, peer_tune, s);
     else if (opt == B2DP_OPT_SGDM)
-      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
+      rc = launch_step_o<B2DP_OPT_SGDM>(p->layout.wire, n, r, a, peer_tune, s);
     else
-      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, Tuning{p->grid_cap, p->peer_unroll, p->peer_vec}, s);
+      rc = launch_step_o<B2DP_OPT_NONE>(p->layout.wire, n, r, a, peer_tune, s);
     if (rc) return rc;
   }
   return B2DP_OK;
@@ -852,6 +869,10 @@ extern "C" int b2dp_plan_set_tuning(b2dp_plan* p, int32_t key, int32_t value) {
       if (value < 1) return fail(B2DP_ERR_INVALID, "set_tuning: grid cap must be >= 1");
       p->mc_bf16_grid_cap = value;
       return B2DP_OK;
+    case B2DP_TUNE_SKIP_OWN:
+      if (value != 0 && value != 1) return fail(B2DP_ERR_INVALID, "set_tuning: skip_own is 0 or 1");
+      p->skip_own = value;
+      return B2DP_OK;
     case B2DP_TUNE_MC_UNROLL:
       if (value != 1 && value != 2 && value != 4) return fail(B2DP_ERR_INVALID, "set_tuning: multicast unroll is 1, 2 or 4");
       p->mc_unroll = value;
@@ -921,20 +942,47 @@ extern "C" int b2dp_pack_step(b2dp_plan* p, int32_t dev, int32_t bucket, const v
                       (!(hyper && hyper->want_stats) || nt * kSubTiles <= kApplyMaxBlocks);
   if (!direct) {
     RankState& r = *rp;
+    const int n = p->ctx->nranks;
+    // Peer path, f32 wire, 256-bit kernel, B2DP_TUNE_SKIP_OWN: rank r's own slice of a bucket is
+    // read by nobody but rank r itself, so it is not packed at all -- the step kernel reads it
+    // where the framework left it (1/n less pack traffic).  Same bits as the packed form.  Off by
+    // default: on 2 x B200 the step kernel lost in the table walk and the cold read what the pack
+    // saved (203.7-210.7 us per call against 205-206 us).
+    const bool own = p->skip_own && n > 1 && !p->ctx->emulated && p->path == B2DP_PATH_PEER &&
+                     p->layout.wire == B2DP_F32 && p->peer_vec == 8 && (n == 2 || n == 4 || n == 8);
+    auto pack_bucket = [&](int b, cudaStream_t ps) -> int {
+      int64_t lo = 0, hi = 0;
+      if (own && p->layout.buckets[b].tile_count <= kOwnMaxTiles) {   // same condition as in run_collective
+        const Bucket& bk = p->layout.buckets[b];
+        lo = bk.offset + (int64_t)r.rank * bk.slice;
+        hi = lo + bk.slice;
+      }
+      return launch_pack<0>(p, r, b, r.grads, grads, p->map.grads, p->layout.wire, prescale, ps, lo, hi);
+    };
+    const float* own_prescale = own ? &prescale : nullptr;
+    cudaStream_t s = (cudaStream_t)stream;
+    DeviceGuard guard(r.device);
     if (r.side && b1 - b0 > 1) {
       // Several buckets, real ranks: the step of bucket b is NVLink-bound and leaves HBM idle, so
       // bucket b+1 is packed underneath it on a side stream.  Same kernels, same arguments, same
       // order of collectives on the caller's stream as the serial form: bit-identical results.
-      cudaStream_t s = (cudaStream_t)stream;
-      DeviceGuard guard(r.device);
       CUDA_TRY(cudaEventRecord(r.ev_start, s));          // gradients exist; earlier steps have read the buckets
       CUDA_TRY(cudaStreamWaitEvent(r.side, r.ev_start, 0));
       bool stats_on = false;
       for (int b = b0; b < b1; ++b) {
-        if (int rc = b2dp_pack(p, dev, b, grads, grad_dtype, prescale, r.side)) return rc;
+        if (int rc = pack_bucket(b, r.side)) return rc;
         CUDA_TRY(cudaEventRecord(r.ev_packed[b], r.side));
         CUDA_TRY(cudaStreamWaitEvent(s, r.ev_packed[b], 0));
-        if (int rc = run_collective(p, dev, b, opt, hyper, 1.0f, 0, stream, stats_on)) return rc;
+        if (int rc = run_collective(p, dev, b, opt, hyper, 1.0f, 0, stream, stats_on, own_prescale)) return rc;
+        stats_on = true;
+      }
+      return B2DP_OK;
+    }
+    if (own) {
+      bool stats_on = false;
+      for (int b = b0; b < b1; ++b) {
+        if (int rc = pack_bucket(b, s)) return rc;
+        if (int rc = run_collective(p, dev, b, opt, hyper, 1.0f, 0, stream, stats_on, own_prescale)) return rc;
         stats_on = true;
       }
       return B2DP_OK;

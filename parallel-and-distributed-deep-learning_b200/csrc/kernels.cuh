@@ -160,7 +160,8 @@ static __global__ void resolve_tiles_kernel(const Tile* __restrict__ tiles, int6
 // list is.  DIR 0: tensors -> flat (cast to WireT, times prescale); DIR 1: flat(f32) -> tensors.
 template <typename WireT, int DIR>
 __global__ void __launch_bounds__(kPackThreads)
-pack_kernel(const TileAbs* __restrict__ tiles, int64_t ntiles, WireT* __restrict__ flat, float prescale) {
+pack_kernel(const TileAbs* __restrict__ tiles, int64_t ntiles, WireT* __restrict__ flat, float prescale,
+            int64_t skip_lo, int64_t skip_hi) {
   // One tile per block: with ~6400 short-lived blocks the hardware scheduler keeps every SM
   // busy and blocks in different phases (loading / storing) overlap, which measured ~10%
   // faster than a persistent grid-stride loop for this pure stream.
@@ -170,6 +171,26 @@ pack_kernel(const TileAbs* __restrict__ tiles, int64_t ntiles, WireT* __restrict
   float* tens = tl.ptr;
   WireT* fl = flat + tl.dst_off;
   const uint32_t count = tl.count;
+  // [skip_lo, skip_hi): flat elements nobody will read from the bucket -- this rank's own slice when
+  // the step kernel reads it in place from the gradient tensors (b2dp_pack_step, peer path): 1/n of
+  // the pack's traffic.  Whole tiles inside the range leave at once; the (at most two) tiles that
+  // straddle a boundary of the range take a plain element loop.
+  if (DIR == 0 && skip_hi > skip_lo) {
+    const int64_t t_lo = tl.dst_off, t_hi = tl.dst_off + count;
+    if (t_lo >= skip_lo && t_hi <= skip_hi) return;
+    if (t_lo < skip_hi && t_hi > skip_lo) {
+      for (uint32_t i = threadIdx.x; i < count; i += kPackThreads) {
+        const int64_t e = t_lo + i;
+        if (e >= skip_lo && e < skip_hi) continue;
+        const float x = __fmul_rn(tens[i], prescale);
+        if (sizeof(WireT) == 4)
+          reinterpret_cast<float*>(fl)[i] = x;
+        else
+          reinterpret_cast<__nv_bfloat16*>(fl)[i] = __float2bfloat16_rn(x);
+      }
+      return;
+    }
+  }
   const uintptr_t addr = reinterpret_cast<uintptr_t>(tens);
   // widest access the tensor's own alignment allows (the flat side is always 128-byte aligned)
   const uint32_t n8 = ((addr & 31) == 0) ? (count >> 3) : 0;              // 256-bit vectors
@@ -308,6 +329,12 @@ struct StepArgs {
   int32_t want_stats;
   int32_t stats_add;         // 1: add to a.stats (a later bucket of the same call) instead of storing
   int32_t push;              // 1: store results to every rank (all-gather); 0: own copy only
+  // own slice read in place (step256_kernel<..., OWN = true>): the bucket's resolved tile table
+  const TileAbs* own_tiles;  // tiles of this bucket, ascending dst_off
+  int32_t own_ntiles;
+  float prescale;            // what pack would have multiplied the gradient by
+  int64_t own_bucket_off;    // flat element offset of the bucket
+  int64_t own_rel8;          // start of this rank's slice inside the bucket, in 8-element units
 };
 
 __device__ __forceinline__ void adam_update(float g, float& w, float& m, float& v, const OptScalars& o) {
@@ -823,22 +850,104 @@ step_mc_bf16_kernel(const StepArgs a) {
 // 256-bit form of the peer-path step (f32 wire): one LDG.E.256 per peer and one STG.E.256 per
 // destination per thread -- half the NVLink requests of the 128-bit form for the same bytes.
 // Same rank-order sum and optimizer arithmetic, so results are bit-identical.
-template <int N, int OPT, int U>
+// This rank's own contribution to vector q of its slice, read where the framework left it.
+// The flat position is looked up in the bucket's tile table: each block first copies the
+// table's keys into shared memory (start of every tile in units of 8 elements relative to the
+// bucket, and its length: 6 bytes per tile, 20 KB for ResNet-50) so the binary search costs a
+// dozen shared-memory reads and hides under the peer loads already in flight -- searched in
+// global memory it cost ~0.3 us per level and made the kernel 20 us slower than packing the
+// slice (r02, 2 x B200).  Elements past the end of a tensor or in alignment padding are zero,
+// and the value is scaled exactly as pack scales it: the sum sees the same bits as if the slice
+// had been packed.
+constexpr int kOwnTileBytes = 14;    // pointer 8 + start 4 + length 2
+constexpr int kOwnMaxTiles = 3400;   // 46.5 KB: stays inside the 48 KB a kernel gets without opting in
+
+struct OwnTable {   // views into the block's dynamic shared memory
+  const float** ptr;
+  uint32_t* rel8;
+  uint16_t* cnt;
+};
+
+__device__ __forceinline__ OwnTable own_table_to_smem(const StepArgs& a, unsigned char* smem) {
+  OwnTable t;
+  t.ptr = reinterpret_cast<const float**>(smem);
+  t.rel8 = reinterpret_cast<uint32_t*>(smem + sizeof(float*) * a.own_ntiles);
+  t.cnt = reinterpret_cast<uint16_t*>(smem + (sizeof(float*) + sizeof(uint32_t)) * a.own_ntiles);
+  for (int i = threadIdx.x; i < a.own_ntiles; i += blockDim.x) {
+    const TileAbs tl = a.own_tiles[i];
+    t.ptr[i] = tl.ptr;
+    t.rel8[i] = (uint32_t)((tl.dst_off - a.own_bucket_off) >> 3);   // tile starts are 32-element aligned
+    t.cnt[i] = (uint16_t)tl.count;
+  }
+  __syncthreads();
+  return t;
+}
+
+__device__ __forceinline__ float8 load_own_f8(const StepArgs& a, const OwnTable& tb, int64_t q) {
+  const uint32_t* rel8 = tb.rel8;
+  const uint16_t* cnt = tb.cnt;
+  const uint32_t e8 = (uint32_t)(a.own_rel8 + q);   // this vector's position in the bucket, in 8-element units
+  int lo = 0, hi = a.own_ntiles;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (rel8[mid] <= e8) lo = mid; else hi = mid;
+  }
+  float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (a.own_ntiles > 0 && e8 >= rel8[lo]) {
+    const uint32_t off = (e8 - rel8[lo]) << 3;
+    const uint32_t count = cnt[lo];
+    if (off < count) {
+      const float* p = tb.ptr[lo] + off;
+      if (count - off >= 8 && (reinterpret_cast<uintptr_t>(p) & 31) == 0) {
+        const float8 t = ld_stream_f8(p);
+        v[0] = t.lo.x; v[1] = t.lo.y; v[2] = t.lo.z; v[3] = t.lo.w; v[4] = t.hi.x; v[5] = t.hi.y; v[6] = t.hi.z; v[7] = t.hi.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (off + i < count) v[i] = p[i];
+      }
+    }
+  }
+  float8 r;
+  r.lo = make_float4(__fmul_rn(v[0], a.prescale), __fmul_rn(v[1], a.prescale), __fmul_rn(v[2], a.prescale), __fmul_rn(v[3], a.prescale));
+  r.hi = make_float4(__fmul_rn(v[4], a.prescale), __fmul_rn(v[5], a.prescale), __fmul_rn(v[6], a.prescale), __fmul_rn(v[7], a.prescale));
+  return r;
+}
+
+template <int N, int OPT, int U, bool OWN = false>
 __global__ void __launch_bounds__(kStepThreads)
 step256_kernel(const StepArgs a) {
+  extern __shared__ __align__(16) unsigned char own_smem[];   // OWN: the bucket's tile table (kOwnTileBytes per tile)
+  OwnTable own_tb = {nullptr, nullptr, nullptr};
+  if (OWN) own_tb = own_table_to_smem(a, own_smem);   // before the barrier: peers are still arriving anyway
   const bool ok = flag_barrier(a.c, 0);
   const int64_t nvec8 = ok ? (a.nvec >> 1) : 0;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float sumsq = 0.0f, bad = 0.0f;
   for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < nvec8; base += stride * U) {
     float8 g[U][N];
+    float8 own[U];   // OWN: this rank's contribution, read in place (g[u][rank] is then never loaded)
     float8 w[U], s0[U], s1[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {   // every NVLink load of the iteration goes out first ...
+      const int64_t q = base + u * stride;
+      if (q < nvec8) {
+#pragma unroll
+        for (int r = 0; r < N; ++r)
+          if (!OWN || r != a.c.rank) g[u][r] = ld_stream_f8(reinterpret_cast<const float*>(a.g[r]) + q * 8);
+      }
+    }
+    if (OWN) {                      // ... the table walks and the local loads hide under them
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t q = base + u * stride;
+        if (q < nvec8) own[u] = load_own_f8(a, own_tb, q);
+      }
+    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t q = base + u * stride;
       if (q < nvec8) {
-#pragma unroll
-        for (int r = 0; r < N; ++r) g[u][r] = ld_stream_f8(reinterpret_cast<const float*>(a.g[r]) + q * 8);
         if (OPT != B2DP_OPT_NONE) {
           w[u] = ld_stream_f8(a.w + q * 8);
           s0[u] = ld_stream_f8(a.s0 + q * 8);
@@ -857,9 +966,11 @@ step256_kernel(const StepArgs a) {
         float* p1 = &s1[u].lo.x;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float acc = (&g[u][0].lo.x)[i];
+          // rank order, whoever's turn it is: a select per term keeps every operand in a register
+          const float own_i = OWN ? (&own[u].lo.x)[i] : 0.0f;
+          float acc = (OWN && a.c.rank == 0) ? own_i : (&g[u][0].lo.x)[i];
 #pragma unroll
-          for (int r = 1; r < N; ++r) acc = __fadd_rn(acc, (&g[u][r].lo.x)[i]);
+          for (int r = 1; r < N; ++r) acc = __fadd_rn(acc, (OWN && a.c.rank == r) ? own_i : (&g[u][r].lo.x)[i]);
           acc = __fmul_rn(acc, a.o.postscale);
           if (a.want_stats) {
             sumsq = fmaf(acc, acc, sumsq);

@@ -597,3 +597,56 @@ def test_missing_peer_times_out_instead_of_hanging():
         assert e.value.code == b200dp._lib.ERR_TIMEOUT
         assert time.time() - t0 < 20
         plan.check(0)                                        # the status word was cleared
+
+
+# ------------------------------------------------------------------ own slice read in place
+@needs2
+@pytest.mark.parametrize("bucket_bytes", [0, 300_000])
+def test_pack_step_reads_the_own_slice_in_place_bit_identically(bucket_bytes):
+    """Peer path, f32 wire: b2dp_pack_step leaves rank r's own slice of every bucket unpacked and the
+    step kernel reads it from the gradient tensors through the tile table.  Ragged, empty and
+    misaligned tensors, a prescale != 1, one and several buckets: same bits as packing everything
+    (skip_own = 0) and as the oracle."""
+    n = 8 if NGPU >= 8 else (4 if NGPU >= 4 else 2)
+    numels = [40000, 7, 0, 1027, 64, 333, 147456, 5, 2048, 70001]
+    N = sum(numels)
+    rng = np.random.default_rng(17)
+    w0 = (rng.standard_normal(N) * 0.05).astype(F)
+    pre = 0.5
+    results = []
+    for skip in (1, 0):
+        ctx = b200dp.Context.local(list(range(n)))
+        ctx.set_timeout(10.0)
+        lay = b200dp.Layout(numels, nranks=n, bucket_bytes=bucket_bytes)
+        plan = b200dp.Plan(ctx, lay)
+        plan.set_tuning(skip_own=skip)
+        for r in range(n):
+            with torch.cuda.device(r):
+                plan.load_weights(r, views(torch.from_numpy(w0).cuda(r), numels))
+        w_ref, m_ref, v_ref = w0.copy(), np.zeros(N, F), np.zeros(N, F)
+        g_rng = np.random.default_rng(23)
+        for s in range(3):
+            hg = [(g_rng.standard_normal(N) * 1e-2).astype(F) for _ in range(n)]
+            # one float of slack in front: every tensor pointer is only 4-byte aligned
+            dg = [torch.from_numpy(np.concatenate([[0.0], g]).astype(F)).cuda(r)[1:] for r, g in enumerate(hg)]
+            for r in range(n):
+                torch.cuda.synchronize(r)
+            h = b200dp.adam_hyper(step=s + 1, want_stats=True)
+            with b200dp.issue_group():
+                for r in range(n):
+                    with torch.cuda.device(r):
+                        plan.pack_step(r, views(dg[r], numels), "adam", h, prescale=pre)
+            oracle.adam_(w_ref, m_ref, v_ref, oracle.addn(hg, prescale=pre), step=s + 1)
+            for r in range(n):
+                torch.cuda.synchronize(r)
+        got = []
+        for r in range(n):
+            with torch.cuda.device(r):
+                plan.check(r)
+            got.append(_flat(plan, lay, numels, b200dp.BUF_WEIGHTS, r))
+            assert np.array_equal(bits(got[-1]), bits(w_ref)), "skip_own=%d rank %d differs from the oracle" % (skip, r)
+        stats = sum(float(plan.tensor(r, b200dp.BUF_STATS).cpu()[0]) for r in range(n))
+        want = oracle.sumsq(oracle.addn(hg, prescale=pre))
+        assert abs(stats - want) <= 1e-6 * want
+        results.append(got[0])
+    assert np.array_equal(bits(results[0]), bits(results[1]))

@@ -56,8 +56,9 @@ def main():
                 configs = []
                 if wire == "f32":
                     configs += [("peer", dict(peer_vec=8, peer_unroll=0, grid_cap=c)) for c in (148, 222, 296)]
+                    configs += [("peer", dict(peer_vec=8, peer_unroll=0, grid_cap=296, skip_own=1))]   # own slice read in place
                     if n == 2:
-                        configs += [("peer", dict(peer_vec=8, peer_unroll=2, grid_cap=c)) for c in (148, 296)]
+                        configs += [("peer", dict(peer_vec=8, peer_unroll=1, grid_cap=296))]
                     if have_mc:
                         configs += [("multicast", dict(mc_unroll=1, mc_grid_cap=c)) for c in (74, 148)]
                 else:
@@ -69,6 +70,7 @@ def main():
                                and c[1].get("mc_grid_cap", 74) == 74 and c[1].get("mc_bf16_grid_cap", 148) == 148]
                 for path, knobs in configs:
                     plan.set_path(path)
+                    plan.set_tuning(skip_own=0)
                     plan.set_tuning(**knobs)
                     us_call = time_all(n, call)
                     us_step = time_all(n, step)
