@@ -152,3 +152,35 @@ def test_rank_context_cross_device_ops_argument_errors():
 
     s = FakeStrategy()
     assert ops.swap_into(s) is s and s.extended._cross_device_ops is ops
+
+
+def _session_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from b200dp import cross_device_ops as cdo
+    eng = cdo.B200CrossDeviceOps(rank=rank, nranks=world, device=0)._engine
+    q.put((rank, eng._session(), eng._session()))
+    dist.destroy_process_group()
+
+
+def test_rank_context_cross_device_ops_agree_on_a_session_two_processes_gloo():
+    """One process per worker (the MWMS shape): the job-unique string the fd exchange needs is agreed
+    through the process group -- same on every rank, different for every plan built."""
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_session_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(30)
+    assert res[0][1] == res[1][1] and res[0][2] == res[1][2] and res[0][1] != res[0][2]
+    with pytest.raises(ValueError, match="session"):
+        cdo.B200CrossDeviceOps(rank=0, nranks=2, device=0)._engine._session()    # no group, no session string
